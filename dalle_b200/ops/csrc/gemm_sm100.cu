@@ -1,0 +1,552 @@
+// bf16 GEMM family for sm_100a: TMA -> 128B-swizzled smem ring -> tcgen05.mma (single-thread issue)
+// -> fp32 accumulators in TMEM (double buffered) -> tcgen05.ld epilogue with fused element-wise work.
+//
+// Replaces the library GEMMs the reference model reaches through ATen/cuBLAS (SURVEY §2.5 K4, K9, K11,
+// K12, K13 and their autograd twins): forward (NT), data-gradient (NN, B read MN-major) and weight-gradient
+// (TN, both operands MN-major, split-K with fp32 red.add into the shared .grad buffer - weight sharing
+// means 16 layers accumulate into one gradient, reference task.py:65-66).
+//
+// Persistent kernel: grid = min(#work units, #SMs); each CTA has 6 warps:
+//   warp 0  : TMA producer            (one lane)
+//   warp 1  : TMEM allocator + MMA issuer (one lane)
+//   warps 2-5: epilogue, warp w owns TMEM lanes 32*(w%4)..+31 (one output row per thread)
+#include "sm100_ptx.cuh"
+#include "b200_api.h"
+
+#include <mutex>
+
+namespace b200 {
+
+constexpr int BM = 128;
+constexpr int BN = 256;
+constexpr int BK = 64;
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
+constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KiB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
+
+struct GemmDev {
+  int M, N, K;         // output M x N, reduction K
+  int m_tiles, n_tiles, splits, kb_total;
+  int tile_n_step;     // 256, or 128 for GEGLU pairing
+  int second_off;      // row offset of the 2nd 128-row B box (128, or n_half for GEGLU)
+  void* out;   long long ldo;
+  void* out2;  long long ldo2;
+  const float* bias;
+  const float* scale;
+  const float* res;  long long ldres;
+  const float2* rot;  // [seq_len][32] (cos, sin) per pair
+  int seq_len;
+  int q_cols;          // columns < q_cols are scaled by q_scale (rotary epilogue)
+  float q_scale;
+  const __nv_bfloat16* aux;  long long ldaux;
+  int n_half;
+  float alpha;
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_erf_grad(float x) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
+  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
+  return cdf + x * pdf;
+}
+
+__device__ __forceinline__ void st_bf16x8(__nv_bfloat16* p, const float* v) {
+  uint4 u;
+  u.x = pack_bf16x2(v[0], v[1]);
+  u.y = pack_bf16x2(v[2], v[3]);
+  u.z = pack_bf16x2(v[4], v[5]);
+  u.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ void ld_bf16x8(const __nv_bfloat16* p, float* v) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  float2 f;
+  f = unpack_bf16x2(u.x); v[0] = f.x; v[1] = f.y;
+  f = unpack_bf16x2(u.y); v[2] = f.x; v[3] = f.y;
+  f = unpack_bf16x2(u.z); v[4] = f.x; v[5] = f.y;
+  f = unpack_bf16x2(u.w); v[6] = f.x; v[7] = f.y;
+}
+__device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+// Write 32 consecutive values of one row as bf16 (guarded on the right edge).
+__device__ __forceinline__ void store_row_bf16(__nv_bfloat16* rowp, int col, int ncols, const float* v) {
+  if (col + 32 <= ncols) {
+#pragma unroll
+    for (int j = 0; j < 32; j += 8) st_bf16x8(rowp + col + j, v + j);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+      if (col + j < ncols) rowp[col + j] = __float2bfloat16(v[j]);
+  }
+}
+
+template <int A_MN, int B_MN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDev g) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  const uint32_t pad = ((raw_addr + 1023u) & ~1023u) - raw_addr;
+  uint8_t* smem = smem_raw + pad;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* full_bar = bars;                 // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;       // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int units = g.m_tiles * g.n_tiles * g.splits;
+  const int kb_per = (g.kb_total + g.splits - 1) / g.splits;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int split = u % g.splits;
+        const int t = u / g.splits;
+        const int n_blk = t % g.n_tiles, m_blk = t / g.n_tiles;
+        const int m0 = m_blk * BM, n0 = n_blk * g.tile_n_step;
+        const int kb0 = split * kb_per;
+        const int kb1 = min(kb0 + kb_per, g.kb_total);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
+          uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
+          const int k0 = kb * BK;
+          if (A_MN == 0) {
+            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);  // box {64 k, 128 m}
+          } else {
+            tma_load_2d(sa, &tmA, &full_bar[stage], m0, k0);  // box {64 m, 64 k}
+            tma_load_2d(sa + 8192, &tmA, &full_bar[stage], m0 + 64, k0);
+          }
+          if (B_MN == 0) {
+            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);  // box {64 k, 128 n}
+            tma_load_2d(sb + 16384, &tmB, &full_bar[stage], k0, n0 + g.second_off);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) tma_load_2d(sb + i * 8192, &tmB, &full_bar[stage], n0 + 64 * i, k0);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
+        const int split = u % g.splits;
+        const int kb0 = split * kb_per;
+        const int kb1 = min(kb0 + kb_per, g.kb_total);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
+          const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            // K-major: 8-row groups 1024 B apart, +32 B per 16-element k step inside the swizzle row.
+            // MN-major: 64-element MN atoms 8192 B apart (LBO), 8-k-row groups 1024 B apart (SBO),
+            //           +2048 B per 16 k rows.
+            const uint64_t ad = A_MN ? make_smem_desc_sw128(sa + kk * 2048, 8192, 1024)
+                                     : make_smem_desc_sw128(sa + kk * 32, 0, 1024);
+            const uint64_t bd = B_MN ? make_smem_desc_sw128(sb + kk * 2048, 8192, 1024)
+                                     : make_smem_desc_sw128(sb + kk * 32, 0, 1024);
+            umma_bf16_ss(tmem_d, ad, bd, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ------------------------------- epilogue warps -------------------------------------------
+    const int q = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+      const int t = u / g.splits;
+      const int n_blk = t % g.n_tiles, m_blk = t / g.n_tiles;
+      const int row = m_blk * BM + q * 32 + lane;
+      const int n0 = n_blk * g.tile_n_step;
+      const bool row_ok = row < g.M;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + acc * BN + (static_cast<uint32_t>(q * 32) << 16);
+
+      if (EPI == B200_EPI_GEGLU) {
+        // accumulator columns [0,128) = value half, [128,256) = gate half (same 128 output columns)
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t ra[32], rg[32];
+          tmem_ld32(taddr + c * 32, ra);
+          tmem_ld32(taddr + 128 + c * 32, rg);
+          tmem_ld_wait();
+          const int col = n0 + c * 32;
+          if (row_ok && col < g.n_half) {
+            float va[32], vg[32], o[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              va[j] = __uint_as_float(ra[j]) + (g.bias ? __ldg(g.bias + col + j) : 0.f);
+              vg[j] = __uint_as_float(rg[j]) + (g.bias ? __ldg(g.bias + g.n_half + col + j) : 0.f);
+              o[j] = va[j] * gelu_erf(vg[j]);
+            }
+            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo, col, g.n_half, o);
+            if (g.out2) {
+              __nv_bfloat16* p2 = reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2;
+              store_row_bf16(p2, col, g.n_half, va);
+              store_row_bf16(p2 + g.n_half, col, g.n_half, vg);
+            }
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          const int col = n0 + c * 32;
+          if (col >= g.N) break;  // warp-uniform
+          uint32_t r[32];
+          tmem_ld32(taddr + c * 32, r);
+          tmem_ld_wait();
+          if (!row_ok) continue;
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          const bool full = col + 32 <= g.N;
+
+          if (EPI == B200_EPI_BF16) {
+            if (g.bias) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] += (col + j < g.N) ? __ldg(g.bias + col + j) : 0.f;
+            }
+            if (g.alpha != 1.0f) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] *= g.alpha;
+            }
+            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo, col, g.N, v);
+          } else if (EPI == B200_EPI_ROTARY) {
+            // interleaved-pair rotary on q, k and v; q additionally scaled (dalle-pytorch applies
+            // rotary to v as well)
+            const int pos = row % g.seq_len;
+            const float2* rt = g.rot + (long long)pos * 32 + ((col & 63) >> 1);
+            const float s = (col < g.q_cols) ? g.q_scale : 1.0f;
+            float o[32];
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float2 cs = __ldg(rt + (j >> 1));
+              const float x0 = v[j] + (g.bias ? __ldg(g.bias + col + j) : 0.f);
+              const float x1 = v[j + 1] + (g.bias ? __ldg(g.bias + col + j + 1) : 0.f);
+              o[j] = (x0 * cs.x - x1 * cs.y) * s;
+              o[j + 1] = (x1 * cs.x + x0 * cs.y) * s;
+            }
+            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo, col, g.N, o);
+          } else if (EPI == B200_EPI_RESID) {
+            // out = res + alpha * scale[col] * (acc + bias[col]); optional bf16 copy of (acc + bias)
+            float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
+            const float* rp = g.res + (long long)row * g.ldres + col;
+            if (full) {
+              float o[32];
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 rr = *reinterpret_cast<const float4*>(rp + j);
+                const float4 sc = __ldg(reinterpret_cast<const float4*>(g.scale + col + j));
+                float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (g.bias) bb = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
+                v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
+                o[j] = rr.x + g.alpha * sc.x * v[j];
+                o[j + 1] = rr.y + g.alpha * sc.y * v[j + 1];
+                o[j + 2] = rr.z + g.alpha * sc.z * v[j + 2];
+                o[j + 3] = rr.w + g.alpha * sc.w * v[j + 3];
+                *reinterpret_cast<float4*>(op + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (col + j < g.N) {
+                  v[j] += g.bias ? g.bias[col + j] : 0.f;
+                  op[j] = rp[j] + g.alpha * g.scale[col + j] * v[j];
+                }
+              }
+            }
+            if (g.out2)
+              store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2, col, g.N, v);
+          } else if (EPI == B200_EPI_GEGLU_BWD) {
+            // acc = d(geglu out); aux = [value_pre | gate_pre] (bf16, ld = ldaux)
+            const __nv_bfloat16* ap = g.aux + (long long)row * g.ldaux + col;
+            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo;
+            float da[32], dg[32];
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                float a8[8], g8[8];
+                ld_bf16x8(ap + j, a8);
+                ld_bf16x8(ap + g.n_half + j, g8);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  da[j + e] = v[j + e] * gelu_erf(g8[e]);
+                  dg[j + e] = v[j + e] * a8[e] * gelu_erf_grad(g8[e]);
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (col + j < g.N) {
+                  const float a = __bfloat162float(ap[j]), gg = __bfloat162float(ap[g.n_half + j]);
+                  da[j] = v[j] * gelu_erf(gg);
+                  dg[j] = v[j] * a * gelu_erf_grad(gg);
+                } else {
+                  da[j] = dg[j] = 0.f;
+                }
+              }
+            }
+            store_row_bf16(op, col, g.N, da);
+            store_row_bf16(op + g.n_half, col, g.N, dg);
+          } else if (EPI == B200_EPI_ATOMIC_F32) {
+            float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                red_add_f32x4(op + j, g.alpha * v[j], g.alpha * v[j + 1], g.alpha * v[j + 2], g.alpha * v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col + j < g.N) atomicAdd(op + j, g.alpha * v[j]);
+            }
+          } else if (EPI == B200_EPI_F32) {
+            float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(op + j) =
+                    make_float4(g.alpha * v[j], g.alpha * v[j + 1], g.alpha * v[j + 2], g.alpha * v[j + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (col + j < g.N) op[j] = g.alpha * v[j];
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// -------------------------------------------------------------------------------------------------
+// host side
+// -------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// Row-major bf16 matrix [rows, cols] with leading dimension ld (elements); box {box_cols, box_rows}.
+int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_cols, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -1;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -1;
+  cuuint64_t gdim[5];
+  cuuint64_t gstr[4];
+  cuuint32_t bx[5];
+  cuuint32_t estr[5];
+  for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; estr[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gdim, gstr, bx, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int A_MN, int B_MN, int EPI>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
+  auto kern = gemm_kernel<A_MN, B_MN, EPI>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
+    if (e != cudaSuccess) return -3;
+    configured = true;
+  }
+  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(ta, tb, g);
+  return cudaGetLastError() == cudaSuccess ? 0 : -4;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
+  if (d->M <= 0 || d->N <= 0 || d->K <= 0) return 0;
+  const int a_mn = (d->mode == B200_GEMM_TN) ? 1 : 0;
+  const int b_mn = (d->mode == B200_GEMM_NT) ? 0 : 1;
+  if ((d->lda % 8) || (d->ldb % 8)) return -10;  // TMA needs 16-byte row strides
+  if (reinterpret_cast<uintptr_t>(d->A) % 16 || reinterpret_cast<uintptr_t>(d->B) % 16) return -11;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn) rc = make_tmap_bf16_2d(&ta, d->A, d->M, d->K, d->lda, 64, 128);
+  else       rc = make_tmap_bf16_2d(&ta, d->A, d->K, d->M, d->lda, 64, 64);
+  if (rc) return rc;
+  const uint64_t b_rows_total = d->epi == B200_EPI_GEGLU ? (uint64_t)2 * d->n_half : (uint64_t)d->N;
+  if (!b_mn) rc = make_tmap_bf16_2d(&tb, d->B, b_rows_total, d->K, d->ldb, 64, 128);
+  else       rc = make_tmap_bf16_2d(&tb, d->B, d->K, d->N, d->ldb, 64, 64);
+  if (rc) return rc;
+
+  GemmDev g;
+  g.M = d->M; g.N = d->N; g.K = d->K;
+  g.kb_total = (d->K + BK - 1) / BK;
+  g.m_tiles = (d->M + BM - 1) / BM;
+  if (d->epi == B200_EPI_GEGLU) {
+    if (b_mn) return -12;
+    g.tile_n_step = 128;
+    g.second_off = d->n_half;
+    g.n_tiles = (d->n_half + 127) / 128;
+  } else {
+    g.tile_n_step = BN;
+    g.second_off = 128;
+    g.n_tiles = (d->N + BN - 1) / BN;
+  }
+  int splits = d->splits;
+  const int tiles = g.m_tiles * g.n_tiles;
+  if (splits <= 0) {
+    splits = 1;
+    if (d->epi == B200_EPI_ATOMIC_F32 && tiles < 2 * num_sms()) {
+      splits = (2 * num_sms() + tiles - 1) / tiles;
+      const int max_splits = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;  // >= 4 k-blocks per unit
+      if (splits > max_splits) splits = max_splits;
+    }
+  }
+  if (splits > 1 && d->epi != B200_EPI_ATOMIC_F32) return -13;
+  if (splits > g.kb_total) splits = g.kb_total;
+  // every split must own >= 1 k-block
+  {
+    const int kb_per = (g.kb_total + splits - 1) / splits;
+    splits = (g.kb_total + kb_per - 1) / kb_per;
+  }
+  g.splits = splits;
+  g.out = d->out; g.ldo = d->ldo;
+  g.out2 = d->out2; g.ldo2 = d->ldo2;
+  g.bias = d->bias; g.scale = d->scale;
+  g.res = d->res; g.ldres = d->ldres;
+  g.rot = reinterpret_cast<const float2*>(d->rot); g.seq_len = d->seq_len > 0 ? d->seq_len : 1;
+  g.q_cols = d->q_cols; g.q_scale = d->q_scale;
+  g.aux = reinterpret_cast<const __nv_bfloat16*>(d->aux); g.ldaux = d->ldaux;
+  g.n_half = d->n_half;
+  g.alpha = d->alpha;
+
+  const int units = tiles * splits;
+  const int grid = units < num_sms() ? units : num_sms();
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+
+#define B200_DISPATCH_EPI(AMN, BMN)                                                              \
+  switch (d->epi) {                                                                              \
+    case B200_EPI_BF16: return launch<AMN, BMN, B200_EPI_BF16>(ta, tb, g, grid, st);             \
+    case B200_EPI_F32: return launch<AMN, BMN, B200_EPI_F32>(ta, tb, g, grid, st);               \
+    case B200_EPI_ATOMIC_F32: return launch<AMN, BMN, B200_EPI_ATOMIC_F32>(ta, tb, g, grid, st); \
+    default: break;                                                                              \
+  }
+  if (d->mode == B200_GEMM_NT) {
+    switch (d->epi) {
+      case B200_EPI_ROTARY: return launch<0, 0, B200_EPI_ROTARY>(ta, tb, g, grid, st);
+      case B200_EPI_RESID: return launch<0, 0, B200_EPI_RESID>(ta, tb, g, grid, st);
+      case B200_EPI_GEGLU: return launch<0, 0, B200_EPI_GEGLU>(ta, tb, g, grid, st);
+      default: break;
+    }
+    B200_DISPATCH_EPI(0, 0)
+  } else if (d->mode == B200_GEMM_NN) {
+    if (d->epi == B200_EPI_GEGLU_BWD) return launch<0, 1, B200_EPI_GEGLU_BWD>(ta, tb, g, grid, st);
+    B200_DISPATCH_EPI(0, 1)
+  } else if (d->mode == B200_GEMM_TN) {
+    B200_DISPATCH_EPI(1, 1)
+  }
+#undef B200_DISPATCH_EPI
+  return -14;
+}

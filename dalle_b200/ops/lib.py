@@ -1,0 +1,103 @@
+"""ctypes loader for the in-tree native libraries (C ABI declared in include/b200_api.h).
+
+The CUDA library is mandatory on a GPU box: ``cuda_lib()`` raises if it is missing so that nothing silently
+falls back to eager PyTorch (the CPU oracle ops live in :mod:`dalle_b200.ops.ref` and are only used for
+CPU tensors).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from pathlib import Path
+
+_HERE = Path(__file__).resolve().parent
+_cuda = None
+_host = None
+launch_count = 0  # number of kernel-launching C-ABI calls made by this process (bench.py reports it)
+
+
+class B200Gemm(ctypes.Structure):
+    _fields_ = [
+        ("mode", ctypes.c_int), ("epi", ctypes.c_int),
+        ("M", ctypes.c_int), ("N", ctypes.c_int), ("K", ctypes.c_int),
+        ("A", ctypes.c_void_p), ("lda", ctypes.c_longlong),
+        ("B", ctypes.c_void_p), ("ldb", ctypes.c_longlong),
+        ("out", ctypes.c_void_p), ("ldo", ctypes.c_longlong),
+        ("out2", ctypes.c_void_p), ("ldo2", ctypes.c_longlong),
+        ("bias", ctypes.c_void_p), ("scale", ctypes.c_void_p),
+        ("res", ctypes.c_void_p), ("ldres", ctypes.c_longlong),
+        ("rot", ctypes.c_void_p),
+        ("seq_len", ctypes.c_int), ("q_cols", ctypes.c_int), ("q_scale", ctypes.c_float),
+        ("aux", ctypes.c_void_p), ("ldaux", ctypes.c_longlong),
+        ("n_half", ctypes.c_int), ("alpha", ctypes.c_float), ("splits", ctypes.c_int),
+    ]
+
+
+def _try_build():
+    if os.environ.get("DALLE_B200_NO_AUTOBUILD"):
+        return
+    try:
+        from . import build
+
+        build.build_all()
+    except Exception as e:  # pragma: no cover - build errors surface when the library is then missing
+        import warnings
+
+        warnings.warn(f"dalle_b200: native build failed: {e}")
+
+
+def cuda_lib() -> ctypes.CDLL:
+    global _cuda
+    if _cuda is None:
+        path = _HERE / "libdalle_b200.so"
+        if not path.exists():
+            _try_build()
+        if not path.exists():
+            raise RuntimeError(
+                f"{path} is missing: build it with `python -m dalle_b200.ops.build` "
+                "(the CUDA ops have no eager fallback on GPU tensors)")
+        _cuda = ctypes.CDLL(str(path))
+        for name in dir(_Sigs):
+            if name.startswith("b200_"):
+                fn = getattr(_cuda, name, None)
+                if fn is not None:
+                    fn.restype = ctypes.c_int
+                    fn.argtypes = getattr(_Sigs, name)
+    return _cuda
+
+
+def host_lib() -> ctypes.CDLL:
+    global _host
+    if _host is None:
+        path = _HERE / "libdalle_b200_host.so"
+        if not path.exists():
+            _try_build()
+        if not path.exists():
+            raise RuntimeError(f"{path} is missing: build it with `python -m dalle_b200.ops.build`")
+        _host = ctypes.CDLL(str(path))
+    return _host
+
+
+def host_lib_available() -> bool:
+    try:
+        host_lib()
+        return True
+    except Exception:
+        return False
+
+
+_p = ctypes.c_void_p
+_i = ctypes.c_int
+_l = ctypes.c_longlong
+_f = ctypes.c_float
+
+
+class _Sigs:
+    b200_gemm_bf16 = [ctypes.POINTER(B200Gemm), _p]
+
+
+def check(rc: int, what: str):
+    global launch_count
+    launch_count += 1
+    if rc != 0:
+        raise RuntimeError(f"{what} failed with code {rc}")
