@@ -1,0 +1,47 @@
+// Shared definitions of the sparse-attention kernels (forward: attn_fwd_sm100.cu, backward: attn_bwd_sm100.cu).
+//
+// The three DALL-E sparsity patterns (dalle-pytorch SparseAxialCausalAttention /
+// SparseConvCausalAttention as configured at reference task.py:63-64) are evaluated as dense 128-query blocks on
+// the tensor cores with an in-register mask:
+//   TEXT : 128 text queries x text keys (causal)
+//   ROW  : 128 image queries (consecutive tokens = 128/F image rows)  x (all text keys + the same 128 tokens)
+//   COL  : 128 image queries enumerated column-major (128/F columns)  x (all text keys + the same 128 tokens)
+//   CONV : 128 image queries (consecutive tokens) x (all text keys + tokens [q0-2F, q0+128))
+// q, k and v arrive already rotated (and q pre-scaled) from the QKV GEMM epilogue.
+#pragma once
+#include "sm100_ptx.cuh"
+
+namespace b200 {
+
+enum { ATT_TEXT = 0, ATT_ROW = 1, ATT_COL = 2, ATT_CONV = 3 };
+
+struct AttnGeom {
+  int B, H;        // batch, heads (dim_head is fixed at 64)
+  int seq;         // tokens per sample in the activations (1280)
+  int T;           // text length incl. <bos> (257)
+  int T_pad;       // T rounded up to 16
+  int F;           // image feature-map side (32)
+  int P;           // F*F image positions (the last one is padding: it has no token)
+  int n_text_blocks, n_img_blocks;
+  int conv_half;   // kernel_size / 2 (2)
+};
+
+// token index (0..seq) of query i of image block `blk`
+template <int MODE>
+__device__ __forceinline__ int img_query_pos(const AttnGeom& g, int blk, int i) {
+  const int pc = blk * 128 + i;
+  if (MODE == ATT_COL) {
+    const int c = pc / g.F, r = pc - c * g.F;
+    return r * g.F + c;
+  }
+  return pc;
+}
+
+// 16-byte chunk address inside a [rows x 64 bf16] 128B-swizzled tile (row pitch 128 B, base 1024-aligned)
+__device__ __forceinline__ uint32_t sw128_offset(int row, int chunk16) {
+  return static_cast<uint32_t>(row) * 128u + (static_cast<uint32_t>(chunk16 ^ (row & 7)) << 4);
+}
+
+constexpr float kLog2e = 1.4426950408889634f;
+
+}  // namespace b200

@@ -1,0 +1,357 @@
+// Sparse DALL-E attention forward on tcgen05 (replaces the einsum/softmax/unfold chain of
+// dalle-pytorch's SparseAxialCausalAttention / SparseConvCausalAttention).
+//
+// One CTA = one (batch, head, 128-query block):
+//   warp 0 : TMA loads of Q, K(text + local), V(text + local) into 128B-swizzled smem
+//   warp 1 : S = Q K^T (tcgen05, fp32 in TMEM, N up to 464 columns)  ...  O = P V
+//   warps 2-5 : masked softmax straight out of TMEM (one query row per thread, two passes), P (bf16) written
+//               into swizzled smem as the A operand of the second MMA; epilogue O/sum -> global, LSE -> global
+#include "attn_common.cuh"
+#include "b200_api.h"
+
+namespace b200 {
+
+int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols,
+                      uint32_t box_rows);
+int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box);
+
+constexpr int ATT_THREADS = 192;
+
+struct AttnFwdArgs {
+  AttnGeom g;
+  __nv_bfloat16* out;   // [B*seq, H*64]
+  float* lse;           // [B, H, seq] (log2 domain)
+  int ld_out;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constant__ CUtensorMap tmTail,
+                const __grid_constant__ CUtensorMap tmAux, const AttnFwdArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  const AttnGeom& g = a.g;
+
+  const int NL = (MODE == ATT_TEXT) ? 0 : (MODE == ATT_CONV ? 128 + 2 * g.F : 128);
+  const int NK = g.T_pad + NL;
+  const int p_blocks = (NK + 63) / 64;
+  const uint32_t qk_bytes = 16384u + static_cast<uint32_t>(NK) * 128u;
+  const uint32_t p_bytes = static_cast<uint32_t>(p_blocks) * 16384u;
+  const uint32_t r1_bytes = qk_bytes > p_bytes ? qk_bytes : p_bytes;
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + 16384;
+  uint8_t* sP = smem;                       // aliases Q|K once S is complete
+  uint8_t* sV = smem + r1_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + static_cast<uint32_t>(NK) * 128u);
+  uint64_t* bar_qk = bars + 0;
+  uint64_t* bar_v = bars + 1;
+  uint64_t* bar_s = bars + 2;
+  uint64_t* bar_p = bars + 3;
+  uint64_t* bar_o = bars + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int blk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int q0 = blk * 128;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tm128);
+    tma_prefetch_desc(&tmTail);
+    tma_prefetch_desc(&tmAux);
+    mbar_init(bar_qk, 1);
+    mbar_init(bar_v, 1);
+    mbar_init(bar_s, 1);
+    mbar_init(bar_p, 128);
+    mbar_init(bar_o, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int row_base = b * g.seq;
+      const int n_full = g.T_pad / 128, tail = g.T_pad % 128;
+      for (int sect = 0; sect < 2; ++sect) {  // 0: Q + K on bar_qk, 1: V on bar_v
+        uint64_t* bar = sect == 0 ? bar_qk : bar_v;
+        uint8_t* dst = sect == 0 ? sK : sV;
+        const int col = (sect == 0 ? g.H * 64 : 2 * g.H * 64) + h * 64;
+        mbar_expect_tx(bar, (sect == 0 ? 16384u : 0u) + static_cast<uint32_t>(NK) * 128u);
+        if (sect == 0) {
+          // queries
+          const int qcol = h * 64;
+          if (MODE == ATT_COL) {
+            const int lines = 128 / g.F;
+            for (int l = 0; l < lines; ++l)
+              tma_load_4d(sQ + l * g.F * 128, &tmAux, bar, qcol, blk * lines + l, 0, b);
+          } else {
+            const int t0 = (MODE == ATT_TEXT) ? q0 : g.T + q0;
+            tma_load_2d(sQ, &tm128, bar, qcol, row_base + t0);
+          }
+        }
+        // text keys / values
+        for (int i = 0; i < n_full; ++i) tma_load_2d(dst + i * 16384, &tm128, bar, col, row_base + i * 128);
+        if (tail) tma_load_2d(dst + n_full * 16384, &tmTail, bar, col, row_base + n_full * 128);
+        // local keys / values
+        uint8_t* dl = dst + g.T_pad * 128;
+        if (MODE == ATT_ROW) {
+          tma_load_2d(dl, &tm128, bar, col, row_base + g.T + q0);
+        } else if (MODE == ATT_COL) {
+          const int lines = 128 / g.F;
+          for (int l = 0; l < lines; ++l) tma_load_4d(dl + l * g.F * 128, &tmAux, bar, col, blk * lines + l, 0, b);
+        } else if (MODE == ATT_CONV) {
+          tma_load_2d(dl, &tmAux, bar, col, row_base + g.T + q0 - 2 * g.F);  // box rows = 2F
+          tma_load_2d(dl + 2 * g.F * 128, &tm128, bar, col, row_base + g.T + q0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      mbar_wait(bar_qk, 0);
+      tc_fence_after();
+      const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK);
+      for (int n0 = 0; n0 < NK; n0 += 256) {
+        const int nsz = min(256, NK - n0);
+        const uint32_t idesc = make_idesc_bf16(128, nsz, 0, 0);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint64_t ad = make_smem_desc_sw128(q_addr + kk * 32, 0, 1024);
+          const uint64_t bd = make_smem_desc_sw128(k_addr + n0 * 128 + kk * 32, 0, 1024);
+          umma_bf16_ss(tmem + n0, ad, bd, idesc, kk > 0 ? 1u : 0u);
+        }
+      }
+      umma_commit(bar_s);
+      // second GEMM once P is in smem
+      mbar_wait(bar_p, 0);
+      mbar_wait(bar_v, 0);
+      tc_fence_after();
+      const uint32_t p_addr = smem_u32(sP), v_addr = smem_u32(sV);
+      const uint32_t idesc2 = make_idesc_bf16(128, 64, 0, 1);
+      for (int k16 = 0; k16 < NK / 16; ++k16) {
+        const uint64_t ad = make_smem_desc_sw128(p_addr + (k16 >> 2) * 16384 + (k16 & 3) * 32, 0, 1024);
+        const uint64_t bd = make_smem_desc_sw128(v_addr + k16 * 2048, 8192, 1024);
+        umma_bf16_ss(tmem, ad, bd, idesc2, k16 > 0 ? 1u : 0u);
+      }
+      umma_commit(bar_o);
+    }
+  } else {
+    const int qw = warp & 3;
+    const int i = qw * 32 + lane;  // query row inside the block
+    const uint32_t trow = tmem + (static_cast<uint32_t>(qw * 32) << 16);
+    // token position of this query
+    int tpos, ip = 0, ir = 0, ic = 0;
+    bool q_valid;
+    if (MODE == ATT_TEXT) {
+      tpos = q0 + i;
+      q_valid = tpos < g.T;
+    } else {
+      ip = img_query_pos<MODE>(g, blk, i);
+      ir = ip / g.F;
+      ic = ip - ir * g.F;
+      tpos = g.T + ip;
+      q_valid = tpos < g.seq;
+    }
+    const int n_text_valid = (MODE == ATT_TEXT) ? min(g.T, tpos + 1) : g.T;
+    const int win0 = qw * 32;  // first local key of this warp's window
+    const int win_chunks = (MODE == ATT_TEXT) ? 0 : (MODE == ATT_CONV ? (32 + 2 * g.F) / 32 : 1);
+
+    auto local_valid = [&](int jl) -> bool {
+      if (MODE == ATT_ROW || MODE == ATT_COL) {
+        return (jl / g.F == i / g.F) && (jl <= i);
+      } else if (MODE == ATT_CONV) {
+        const int kp = q0 - 2 * g.F + jl;
+        if (kp < 0 || kp > ip) return false;
+        const int kr = kp / g.F, kc = kp - kr * g.F;
+        const int dr = ir - kr, dc = ic - kc;
+        return dr <= g.conv_half && dc <= g.conv_half && dc >= -g.conv_half;
+      }
+      return false;
+    };
+
+    mbar_wait(bar_s, 0);
+    tc_fence_after();
+
+    // ---- pass 1: row maximum (log2 domain) ----
+    float mx = -1e30f;
+    for (int c0 = 0; c0 < g.T_pad; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(trow + c0, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c0 + j < n_text_valid) mx = fmaxf(mx, __uint_as_float(r[j]));
+    }
+    for (int wc = 0; wc < win_chunks; ++wc) {
+      uint32_t r[32];
+      tmem_ld32(trow + g.T_pad + win0 + wc * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (local_valid(win0 + wc * 32 + j)) mx = fmaxf(mx, __uint_as_float(r[j]));
+    }
+    const float mxs = mx * kLog2e;
+
+    // ---- pass 2: p = exp2(s*log2e - max), row sum, bf16 P -> swizzled smem ----
+    float sum = 0.f;
+    auto emit8 = [&](int key0, const float* p8) {
+      uint4 u;
+      u.x = pack_bf16x2(p8[0], p8[1]);
+      u.y = pack_bf16x2(p8[2], p8[3]);
+      u.z = pack_bf16x2(p8[4], p8[5]);
+      u.w = pack_bf16x2(p8[6], p8[7]);
+      *reinterpret_cast<uint4*>(sP + (key0 >> 6) * 16384 + sw128_offset(i, (key0 & 63) >> 3)) = u;
+    };
+    for (int c0 = 0; c0 < g.T_pad; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(trow + c0, r);
+      tmem_ld_wait();
+      float p[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float e = exp2f(__uint_as_float(r[j]) * kLog2e - mxs);
+        p[j] = (c0 + j < n_text_valid) ? e : 0.f;
+        sum += p[j];
+      }
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq)
+        if (c0 + gq * 8 < g.T_pad) emit8(c0 + gq * 8, p + gq * 8);
+    }
+    if (MODE != ATT_TEXT) {
+      // zero the local columns outside this warp's window
+      const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int j0 = 0; j0 < NL; j0 += 8)
+        if (j0 < win0 || j0 >= win0 + win_chunks * 32) emit8(g.T_pad + j0, z8);
+      for (int wc = 0; wc < win_chunks; ++wc) {
+        uint32_t r[32];
+        const int jl0 = win0 + wc * 32;
+        tmem_ld32(trow + g.T_pad + jl0, r);
+        tmem_ld_wait();
+        float p[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float e = exp2f(__uint_as_float(r[j]) * kLog2e - mxs);
+          p[j] = local_valid(jl0 + j) ? e : 0.f;
+          sum += p[j];
+        }
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) emit8(g.T_pad + jl0 + gq * 8, p + gq * 8);
+      }
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    mbar_arrive(bar_p);
+
+    // ---- epilogue: O / sum ----
+    mbar_wait(bar_o, 0);
+    tc_fence_after();
+    const float inv = sum > 0.f ? 1.0f / sum : 0.f;
+    __nv_bfloat16* orow = a.out + static_cast<long long>(b * g.seq + tpos) * a.ld_out + h * 64;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t r[32];
+      tmem_ld32(trow + c * 32, r);
+      tmem_ld_wait();
+      if (q_valid) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          uint4 u;
+          u.x = pack_bf16x2(__uint_as_float(r[j]) * inv, __uint_as_float(r[j + 1]) * inv);
+          u.y = pack_bf16x2(__uint_as_float(r[j + 2]) * inv, __uint_as_float(r[j + 3]) * inv);
+          u.z = pack_bf16x2(__uint_as_float(r[j + 4]) * inv, __uint_as_float(r[j + 5]) * inv);
+          u.w = pack_bf16x2(__uint_as_float(r[j + 6]) * inv, __uint_as_float(r[j + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + c * 32 + j) = u;
+        }
+      }
+    }
+    if (q_valid) a.lse[(static_cast<long long>(b) * g.H + h) * g.seq + tpos] = mxs + log2f(sum);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+static size_t attn_fwd_smem(const AttnGeom& g, int mode) {
+  const int NL = mode == ATT_TEXT ? 0 : (mode == ATT_CONV ? 128 + 2 * g.F : 128);
+  const int NK = g.T_pad + NL;
+  const size_t qk = 16384 + (size_t)NK * 128, p = (size_t)((NK + 63) / 64) * 16384;
+  return (qk > p ? qk : p) + (size_t)NK * 128 + 64 + 1024;
+}
+
+template <int MODE>
+static int launch_fwd(const CUtensorMap& t128, const CUtensorMap& ttail, const CUtensorMap& taux,
+                      const AttnFwdArgs& a, int nblocks, cudaStream_t st) {
+  auto kern = attn_fwd_kernel<MODE>;
+  const size_t smem = attn_fwd_smem(a.g, MODE);
+  if (smem > 227 * 1024) return -20;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return -21;
+  dim3 grid(nblocks, a.g.H, a.g.B);
+  kern<<<grid, ATT_THREADS, smem, st>>>(t128, ttail, taux, a);
+  return cudaGetLastError() == cudaSuccess ? 0 : -22;
+}
+
+int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
+                   CUtensorMap* taux) {
+  const uint64_t rows = (uint64_t)g.B * g.seq, cols = 3ull * g.H * 64;
+  int rc = make_tmap_bf16_2d(t128, qkv, rows, cols, cols, 64, 128);
+  if (rc) return rc;
+  const int tail = g.T_pad % 128;
+  rc = make_tmap_bf16_2d(ttail, qkv, rows, cols, cols, 64, tail ? tail : 128);
+  if (rc) return rc;
+  if (mode == ATT_COL) {
+    // image part viewed as [b][r][c][feature]; one box = one image column (F tokens, stride F rows)
+    const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(qkv) + (size_t)g.T * cols;
+    // the last image position has no token: rows r = F-1 expose F-1 columns only for the last sample -> the
+    // tensor map is declared over the full grid; reads past the allocation are avoided by bounding dim 3 (batch)
+    // and letting the final element fall into the next sample / OOB fill.
+    uint64_t dims[4] = {cols, (uint64_t)g.F, (uint64_t)g.F, (uint64_t)g.B};
+    uint64_t strides[3] = {cols * 2, cols * 2 * g.F, cols * 2 * g.seq};
+    uint32_t box[4] = {64, 1, (uint32_t)g.F, 1};
+    rc = make_tmap_bf16_nd(taux, base, 4, dims, strides, box);
+  } else {
+    rc = make_tmap_bf16_2d(taux, qkv, rows, cols, cols, 64, 2 * g.F);
+  }
+  return rc;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
+                             int conv_kernel, void* stream) {
+  AttnGeom g;
+  g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
+  g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = conv_kernel / 2;
+  if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  AttnFwdArgs a;
+  a.g = g; a.out = reinterpret_cast<__nv_bfloat16*>(out); a.lse = lse; a.ld_out = H * 64;
+  CUtensorMap t128, ttail, taux;
+  // text -> text
+  int rc = attn_make_maps(qkv, g, ATT_TEXT, &t128, &ttail, &taux);
+  if (rc) return rc;
+  rc = launch_fwd<ATT_TEXT>(t128, ttail, taux, a, g.n_text_blocks, st);
+  if (rc) return rc;
+  // image -> text + local
+  rc = attn_make_maps(qkv, g, mode, &t128, &ttail, &taux);
+  if (rc) return rc;
+  switch (mode) {
+    case ATT_ROW: return launch_fwd<ATT_ROW>(t128, ttail, taux, a, g.n_img_blocks, st);
+    case ATT_COL: return launch_fwd<ATT_COL>(t128, ttail, taux, a, g.n_img_blocks, st);
+    case ATT_CONV: return launch_fwd<ATT_CONV>(t128, ttail, taux, a, g.n_img_blocks, st);
+    default: return -31;
+  }
+}

@@ -53,6 +53,15 @@ typedef struct B200Gemm {
 
 int b200_gemm_bf16(const B200Gemm* desc, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Sparse DALL-E attention (tcgen05).  qkv: bf16 [B*seq (+1 padding row), 3*H*64] = [q | k | v], already rotated and
+ * q pre-scaled (B200_EPI_ROTARY).  mode: 1 = axial_row, 2 = axial_col, 3 = conv_like (text->text causal attention
+ * is always included).  out: bf16 [B*seq, H*64]; lse: fp32 [B, H, seq] (log2 domain, consumed by the backward).
+ * Replaces dalle-pytorch SparseAxialCausalAttention / SparseConvCausalAttention (reference task.py:63-64).
+ * ---------------------------------------------------------------------------------------------- */
+int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
+                  int conv_kernel, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
