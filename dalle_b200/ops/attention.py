@@ -53,3 +53,43 @@ def attn_fwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, cfg: Dalle
     lib.check(rc, "b200_attn_fwd")
     lib.launch_count += 1  # two kernels per call (text block + image block)
     return out
+
+
+def inv_rotary_scale(d_rot: torch.Tensor, rot_pairs: torch.Tensor, cfg: DalleConfig, q_scale: float) -> torch.Tensor:
+    """Transpose of the QKV epilogue (rotary on q,k,v + q scale): gradient w.r.t. the raw projection output."""
+    M, C = d_rot.shape
+    pos = torch.arange(M, device=d_rot.device) % cfg.seq_len
+    cs = rot_pairs[pos].to(d_rot.device)
+    cos, sin = cs[:, None, :, 0], cs[:, None, :, 1]
+    x = d_rot.float().view(M, C // 64, 32, 2)
+    x0, x1 = x[..., 0], x[..., 1]
+    out = torch.stack((x0 * cos + x1 * sin, x1 * cos - x0 * sin), dim=-1).view(M, C).clone()
+    out[:, : cfg.inner_dim] *= q_scale
+    return out
+
+
+def attn_bwd_ref(qkv, d_out, cfg: DalleConfig, attn_type: str, rot_pairs, q_scale):
+    M = d_out.shape[0]
+    x = qkv[:M].detach().float().requires_grad_(True)
+    with torch.enable_grad():
+        o, _ = attn_core_ref(x, cfg, attn_type)
+    (d_rot,) = torch.autograd.grad(o, x, d_out[:M].float())
+    return inv_rotary_scale(d_rot, rot_pairs, cfg, q_scale)
+
+
+def attn_bwd(qkv, out, d_out, lse, delta, dqkv, kv_acc, rot_pairs, cfg: DalleConfig, attn_type: str):
+    """dqkv <- gradient w.r.t. the raw QKV projection.  GPU: d_out needs a padding row like qkv; kv_acc must be
+    zero on entry (it is returned zeroed)."""
+    q_scale = cfg.dim_head ** -0.5
+    if not qkv.is_cuda:
+        dqkv.copy_(attn_bwd_ref(qkv, d_out, cfg, attn_type, rot_pairs, q_scale).to(dqkv.dtype))
+        return dqkv
+    B = out.shape[0] // cfg.seq_len
+    rc = lib.cuda_lib().b200_attn_bwd(qkv.data_ptr(), out.data_ptr(), d_out.data_ptr(), lse.data_ptr(),
+                                      delta.data_ptr(), dqkv.data_ptr(), kv_acc.data_ptr(), rot_pairs.data_ptr(),
+                                      q_scale, B, cfg.heads, cfg.seq_len, cfg.text_len, cfg.image_fmap_size,
+                                      ATTN_TYPE_CODES[attn_type] + 1, cfg.conv_kernel_size,
+                                      torch.cuda.current_stream().cuda_stream)
+    lib.check(rc, "b200_attn_bwd")
+    lib.launch_count += 3  # delta + text blocks + image blocks + finish
+    return dqkv

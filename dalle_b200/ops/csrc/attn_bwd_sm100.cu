@@ -1,0 +1,461 @@
+// Sparse DALL-E attention backward on tcgen05 (backward halves).
+//
+// One CTA = one (batch, head, 128-query block); it walks the 128-key chunks that block can see
+// (text chunks, then its local chunk(s)) and per chunk runs five MMAs:
+//     S = Q K^T        dP = dO V^T                         (recompute / dgrad of PV)
+//     P = exp2(S*log2e - lse) (masked),  dS = P * (dP - delta)   (softmax warps, TMEM -> regs -> swizzled smem)
+//     dQ += dS K       dK = dS^T Q       dV = P^T dO        (accumulators in TMEM)
+// dQ is written once at the end (inverse rotary + q scale applied, bf16, straight into d_qkv).
+// dK/dV of an axial block's own local chunk are exclusive to the CTA -> inverse rotary + bf16 store.
+// dK/dV of text keys (and of conv_like local keys) are shared between CTAs -> fp32 red.add into `kv_acc`
+// (rot-domain), which b200_attn_bwd_finish converts (inverse rotary, bf16) and clears.
+#include "attn_common.cuh"
+#include "b200_api.h"
+
+namespace b200 {
+
+int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols,
+                      uint32_t box_rows);
+int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box);
+int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
+                   CUtensorMap* taux);
+
+constexpr int ATTB_THREADS = 192;
+
+struct AttnBwdArgs {
+  AttnGeom g;
+  const float* lse;     // [B,H,seq] log2 domain
+  const float* delta;   // [B,H,seq] rowsum(dO * O)
+  __nv_bfloat16* dqkv;  // [B*seq, 3*H*64]
+  float* kv_acc;        // [B*seq, 2*H*64] fp32, zero on entry
+  const float2* rot;    // [seq+1][32] (cos, sin)
+  float q_scale;
+};
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// v[0..31] = 32 consecutive head dims starting at d0 (0 or 32) -> inverse rotation by the position's angles
+__device__ __forceinline__ void inv_rotary32(float* v, const float2* rot_row, int d0, float scale) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 2) {
+    const float2 cs = __ldg(rot_row + ((d0 + j) >> 1));
+    const float x0 = v[j], x1 = v[j + 1];
+    v[j] = (x0 * cs.x + x1 * cs.y) * scale;
+    v[j + 1] = (x1 * cs.x - x0 * cs.y) * scale;
+  }
+}
+
+__device__ __forceinline__ void store32_bf16(__nv_bfloat16* p, const float* v) {
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    uint4 u;
+    u.x = pack_bf16x2(v[j], v[j + 1]);
+    u.y = pack_bf16x2(v[j + 2], v[j + 3]);
+    u.z = pack_bf16x2(v[j + 4], v[j + 5]);
+    u.w = pack_bf16x2(v[j + 6], v[j + 7]);
+    *reinterpret_cast<uint4*>(p + j) = u;
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(ATTB_THREADS, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmQKVcol,
+                const __grid_constant__ CUtensorMap tmDO, const __grid_constant__ CUtensorMap tmDOcol,
+                const AttnBwdArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  const AttnGeom& g = a.g;
+  uint8_t* sQ = smem;
+  uint8_t* sDO = smem + 16384;
+  uint8_t* sK = smem + 32768;        // 2 stages x 16 KiB
+  uint8_t* sV = smem + 65536;        // 2 stages x 16 KiB
+  uint8_t* sP = smem + 98304;        // 32 KiB  [128 q][128 keys] as two 64-key K-major tiles
+  uint8_t* sDS = smem + 131072;      // 32 KiB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 163840);
+  uint64_t* bar_q = bars + 0;
+  uint64_t* kv_full = bars + 1;   // [2]
+  uint64_t* kv_empty = bars + 3;  // [2]
+  uint64_t* bar_s = bars + 5;
+  uint64_t* bar_pds = bars + 6;
+  uint64_t* bar_mma2 = bars + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int blk = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int q0 = blk * 128;
+  const int HD = g.H * 64;
+
+  // chunk schedule
+  const int n_text_chunks = (MODE == ATT_TEXT) ? min(blk + 1, (g.T + 127) / 128) : (g.T + 127) / 128;
+  const int n_local_chunks = (MODE == ATT_TEXT) ? 0 : (MODE == ATT_CONV ? 2 : 1);
+  const int n_chunks = n_text_chunks + n_local_chunks;
+
+  if (warp == 0 && lane == 0) {
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    mbar_init(bar_s, 1);
+    mbar_init(bar_pds, 128);
+    mbar_init(bar_mma2, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DQ = 256, TM_DK = 320, TM_DV = 384;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int row_base = b * g.seq;
+      const int lines = 128 / g.F;
+      // Q and dO
+      mbar_expect_tx(bar_q, 32768);
+      if (MODE == ATT_COL) {
+        for (int l = 0; l < lines; ++l) {
+          tma_load_4d(sQ + l * g.F * 128, &tmQKVcol, bar_q, h * 64, blk * lines + l, 0, b);
+          tma_load_4d(sDO + l * g.F * 128, &tmDOcol, bar_q, h * 64, blk * lines + l, 0, b);
+        }
+      } else {
+        const int t0 = (MODE == ATT_TEXT) ? q0 : g.T + q0;
+        tma_load_2d(sQ, &tmQKV, bar_q, h * 64, row_base + t0);
+        tma_load_2d(sDO, &tmDO, bar_q, h * 64, row_base + t0);
+      }
+      for (int c = 0; c < n_chunks; ++c) {
+        const int s = c & 1;
+        const uint32_t ph = (c >> 1) & 1;
+        mbar_wait(&kv_empty[s], ph ^ 1);
+        mbar_expect_tx(&kv_full[s], 32768);
+        uint8_t* dk = sK + s * 16384;
+        uint8_t* dv = sV + s * 16384;
+        const int kcol = HD + h * 64, vcol = 2 * HD + h * 64;
+        if (c < n_text_chunks) {
+          tma_load_2d(dk, &tmQKV, &kv_full[s], kcol, row_base + c * 128);
+          tma_load_2d(dv, &tmQKV, &kv_full[s], vcol, row_base + c * 128);
+        } else {
+          const int lc = c - n_text_chunks;
+          if (MODE == ATT_COL) {
+            for (int l = 0; l < lines; ++l) {
+              tma_load_4d(dk + l * g.F * 128, &tmQKVcol, &kv_full[s], kcol, blk * lines + l, 0, b);
+              tma_load_4d(dv + l * g.F * 128, &tmQKVcol, &kv_full[s], vcol, blk * lines + l, 0, b);
+            }
+          } else {
+            const int t0 = (MODE == ATT_CONV) ? g.T + q0 - 2 * g.F + lc * 128 : g.T + q0;
+            tma_load_2d(dk, &tmQKV, &kv_full[s], kcol, row_base + t0);
+            tma_load_2d(dv, &tmQKV, &kv_full[s], vcol, row_base + t0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      mbar_wait(bar_q, 0);
+      const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO), p_addr = smem_u32(sP), ds_addr = smem_u32(sDS);
+      constexpr uint32_t id_s = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t id_dq = make_idesc_bf16(128, 64, 0, 1);
+      constexpr uint32_t id_dkv = make_idesc_bf16(128, 64, 1, 1);
+      for (int c = 0; c < n_chunks; ++c) {
+        const int s = c & 1;
+        const uint32_t ph = (c >> 1) & 1;
+        mbar_wait(&kv_full[s], ph);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(sK + s * 16384), v_addr = smem_u32(sV + s * 16384);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16_ss(tmem + TM_S, make_smem_desc_sw128(q_addr + kk * 32, 0, 1024),
+                       make_smem_desc_sw128(k_addr + kk * 32, 0, 1024), id_s, kk > 0);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+          umma_bf16_ss(tmem + TM_DP, make_smem_desc_sw128(do_addr + kk * 32, 0, 1024),
+                       make_smem_desc_sw128(v_addr + kk * 32, 0, 1024), id_s, kk > 0);
+        umma_commit(bar_s);
+        mbar_wait(bar_pds, c & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k16 = 0; k16 < 8; ++k16) {
+          // dQ += dS K   (A = dS K-major over keys; B = K read MN-major: N = 64 dims, K = keys)
+          umma_bf16_ss(tmem + TM_DQ, make_smem_desc_sw128(ds_addr + (k16 >> 2) * 16384 + (k16 & 3) * 32, 0, 1024),
+                       make_smem_desc_sw128(k_addr + k16 * 2048, 8192, 1024), id_dq, (c > 0 || k16 > 0));
+        }
+        {
+#pragma unroll
+          for (int k16 = 0; k16 < 8; ++k16) {
+            // dV = P^T dO, dK = dS^T Q  (A read MN-major: M = keys, K = queries; B MN-major)
+            umma_bf16_ss(tmem + TM_DV, make_smem_desc_sw128(p_addr + k16 * 2048, 16384, 1024),
+                         make_smem_desc_sw128(do_addr + k16 * 2048, 8192, 1024), id_dkv, k16 > 0);
+            umma_bf16_ss(tmem + TM_DK, make_smem_desc_sw128(ds_addr + k16 * 2048, 16384, 1024),
+                         make_smem_desc_sw128(q_addr + k16 * 2048, 8192, 1024), id_dkv, k16 > 0);
+          }
+        }
+        umma_commit(&kv_empty[s]);
+        umma_commit(bar_mma2);
+      }
+    }
+  } else {
+    const int qw = warp & 3;
+    const int i = qw * 32 + lane;
+    const uint32_t trow = tmem + (static_cast<uint32_t>(qw * 32) << 16);
+    int tpos, ip = 0, ir = 0, ic = 0;
+    bool q_valid;
+    if (MODE == ATT_TEXT) {
+      tpos = q0 + i;
+      q_valid = tpos < g.T;
+    } else {
+      ip = img_query_pos<MODE>(g, blk, i);
+      ir = ip / g.F;
+      ic = ip - ir * g.F;
+      tpos = g.T + ip;
+      q_valid = tpos < g.seq;
+    }
+    const long long bh = static_cast<long long>(b) * g.H + h;
+    const float lse_i = q_valid ? a.lse[bh * g.seq + tpos] : 0.f;
+    const float delta_i = q_valid ? a.delta[bh * g.seq + tpos] : 0.f;
+    const int win0 = qw * 32;
+
+    for (int c = 0; c < n_chunks; ++c) {
+      const bool is_text = c < n_text_chunks;
+      const int lc = c - n_text_chunks;
+      mbar_wait(bar_s, c & 1);
+      tc_fence_after();
+      // ---- P and dS for this chunk ----
+#pragma unroll 1
+      for (int cc = 0; cc < 4; ++cc) {
+        const int j0 = cc * 32;
+        bool any = q_valid;
+        if (any && !is_text) {
+          if (MODE == ATT_ROW || MODE == ATT_COL) any = (j0 == win0);
+          if (MODE == ATT_CONV) {
+            const int jg0 = lc * 128 + j0;  // global local-key index of this 32-column group
+            any = (jg0 + 32 > win0) && (jg0 < win0 + 32 + 2 * g.F);
+          }
+        }
+        float p[32], ds[32];
+        if (__any_sync(0xffffffffu, any)) {
+          uint32_t rs[32], rp[32];
+          tmem_ld32(trow + TM_S + j0, rs);
+          tmem_ld32(trow + TM_DP + j0, rp);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            bool valid;
+            const int jj = j0 + j;
+            if (is_text) {
+              const int kt = c * 128 + jj;
+              valid = (MODE == ATT_TEXT) ? (kt <= tpos) : (kt < g.T);
+            } else if (MODE == ATT_ROW || MODE == ATT_COL) {
+              valid = (jj / g.F == i / g.F) && (jj <= i);
+            } else {
+              const int kp = q0 - 2 * g.F + lc * 128 + jj;
+              valid = false;
+              if (kp >= 0 && kp <= ip) {
+                const int kr = kp / g.F, kc = kp - kr * g.F;
+                valid = (ir - kr <= g.conv_half) && (ic - kc <= g.conv_half) && (kc - ic <= g.conv_half);
+              }
+            }
+            valid = valid && any;
+            const float pe = exp2f(__uint_as_float(rs[j]) * kLog2e - lse_i);
+            p[j] = valid ? pe : 0.f;
+            ds[j] = valid ? pe * (__uint_as_float(rp[j]) - delta_i) : 0.f;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { p[j] = 0.f; ds[j] = 0.f; }
+        }
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          const int key0 = j0 + gq * 8;
+          const uint32_t off = (key0 >> 6) * 16384 + sw128_offset(i, (key0 & 63) >> 3);
+          uint4 u;
+          u.x = pack_bf16x2(p[gq * 8 + 0], p[gq * 8 + 1]);
+          u.y = pack_bf16x2(p[gq * 8 + 2], p[gq * 8 + 3]);
+          u.z = pack_bf16x2(p[gq * 8 + 4], p[gq * 8 + 5]);
+          u.w = pack_bf16x2(p[gq * 8 + 6], p[gq * 8 + 7]);
+          *reinterpret_cast<uint4*>(sP + off) = u;
+          u.x = pack_bf16x2(ds[gq * 8 + 0], ds[gq * 8 + 1]);
+          u.y = pack_bf16x2(ds[gq * 8 + 2], ds[gq * 8 + 3]);
+          u.z = pack_bf16x2(ds[gq * 8 + 4], ds[gq * 8 + 5]);
+          u.w = pack_bf16x2(ds[gq * 8 + 6], ds[gq * 8 + 7]);
+          *reinterpret_cast<uint4*>(sDS + off) = u;
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(bar_pds);
+
+      // ---- dK / dV of this chunk (thread = key row i of the chunk) ----
+      mbar_wait(bar_mma2, c & 1);
+      tc_fence_after();
+      int ktok;  // token index of key row i, -1 if it must not be written
+      bool direct = false;
+      if (is_text) {
+        const int kt = c * 128 + i;
+        ktok = kt < g.T ? kt : -1;
+      } else if (MODE == ATT_ROW || MODE == ATT_COL) {
+        ktok = q_valid ? tpos : -1;  // the block's own tokens, same enumeration as the queries
+        direct = true;
+      } else {
+        const int kp = q0 - 2 * g.F + lc * 128 + i;
+        ktok = (kp >= 0 && kp < g.P - 1 && kp < q0 + 128) ? g.T + kp : -1;
+      }
+#pragma unroll 1
+      for (int half = 0; half < 4; ++half) {  // 0,1: dK dims 0-31 / 32-63 ; 2,3: dV
+        const bool is_v = half >= 2;
+        const int d0 = (half & 1) * 32;
+        uint32_t r[32];
+        tmem_ld32(trow + (is_v ? TM_DV : TM_DK) + d0, r);
+        tmem_ld_wait();
+        if (ktok < 0) continue;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        const long long grow = static_cast<long long>(b) * g.seq + ktok;
+        if (direct) {
+          inv_rotary32(v, a.rot + static_cast<long long>(ktok) * 32, d0, 1.0f);
+          store32_bf16(a.dqkv + grow * (3 * HD) + (is_v ? 2 : 1) * HD + h * 64 + d0, v);
+        } else {
+          float* dst = a.kv_acc + grow * (2 * HD) + (is_v ? HD : 0) + h * 64 + d0;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+      }
+      tc_fence_before();
+    }
+
+    // ---- dQ ----
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      uint32_t r[32];
+      tmem_ld32(trow + TM_DQ + half * 32, r);
+      tmem_ld_wait();
+      if (!q_valid) continue;
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+      inv_rotary32(v, a.rot + static_cast<long long>(tpos) * 32, half * 32, a.q_scale);
+      store32_bf16(a.dqkv + (static_cast<long long>(b) * g.seq + tpos) * (3 * HD) + h * 64 + half * 32, v);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]        (one warp per (row, head) pair group)
+__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                  float* __restrict__ delta, int rows, int H, int seq) {
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (gw >= rows * H) return;
+  const int row = gw / H, h = gw - row * H;
+  const long long off = static_cast<long long>(row) * H * 64 + h * 64 + lane * 2;
+  const float2 x = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(o + off));
+  const float2 y = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(d_o + off));
+  const float s = warp_sum(x.x * y.x + x.y * y.y);
+  if (lane == 0) {
+    const int b = row / seq, t = row - b * seq;
+    delta[(static_cast<long long>(b) * H + h) * seq + t] = s;
+  }
+}
+
+// kv_acc (fp32, rot domain) -> inverse rotary -> bf16 into d_qkv k/v sections; clears kv_acc.
+// rows_per_sample = T (axial: only text keys went through the accumulator) or seq (conv_like).
+__global__ void attn_bwd_finish_kernel(float* __restrict__ kv_acc, __nv_bfloat16* __restrict__ dqkv,
+                                       const float2* __restrict__ rot, int B, int seq, int rows_per_sample, int HD) {
+  const int pairs_per_row = HD;  // (k,v) x HD/2 pairs
+  const long long total = static_cast<long long>(B) * rows_per_sample * pairs_per_row;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int pr = static_cast<int>(idx % pairs_per_row);
+    const long long rr = idx / pairs_per_row;
+    const int t = static_cast<int>(rr % rows_per_sample), b = static_cast<int>(rr / rows_per_sample);
+    const long long grow = static_cast<long long>(b) * seq + t;
+    const int col = pr * 2;            // column inside [k | v] (2*HD wide)
+    float2* src = reinterpret_cast<float2*>(kv_acc + grow * (2 * HD) + col);
+    const float2 x = *src;
+    *src = make_float2(0.f, 0.f);
+    const float2 cs = __ldg(rot + static_cast<long long>(t) * 32 + ((col & 63) >> 1));
+    const float o0 = x.x * cs.x + x.y * cs.y, o1 = x.y * cs.x - x.x * cs.y;
+    *reinterpret_cast<uint32_t*>(dqkv + grow * (3 * HD) + HD + col) = pack_bf16x2(o0, o1);
+  }
+}
+
+template <int MODE>
+static int launch_bwd(const CUtensorMap& t1, const CUtensorMap& t2, const CUtensorMap& t3, const CUtensorMap& t4,
+                      const AttnBwdArgs& a, int nblocks, cudaStream_t st) {
+  auto kern = attn_bwd_kernel<MODE>;
+  const int smem = 163840 + 128 + 1024;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return -21;
+  dim3 grid(nblocks, a.g.H, a.g.B);
+  kern<<<grid, ATTB_THREADS, smem, st>>>(t1, t2, t3, t4, a);
+  return cudaGetLastError() == cudaSuccess ? 0 : -22;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                             void* dqkv, float* kv_acc, const void* rot, float q_scale, int B, int H, int seq, int T,
+                             int F, int mode, int conv_kernel, void* stream) {
+  AttnGeom g;
+  g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
+  g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = conv_kernel / 2;
+  if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int HD = H * 64;
+  {
+    const long long warps = static_cast<long long>(B) * seq * H;
+    const int threads = 256;
+    const long long blocks = (warps * 32 + threads - 1) / threads;
+    attn_delta_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(
+        reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B * seq, H,
+        seq);
+  }
+  AttnBwdArgs a;
+  a.g = g; a.lse = lse; a.delta = delta; a.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv); a.kv_acc = kv_acc;
+  a.rot = reinterpret_cast<const float2*>(rot); a.q_scale = q_scale;
+
+  CUtensorMap tq, ttail, tqcol, tdo, tdocol;
+  int rc = attn_make_maps(qkv, g, ATT_COL, &tq, &ttail, &tqcol);
+  if (rc) return rc;
+  const uint64_t rows = (uint64_t)B * seq;
+  rc = make_tmap_bf16_2d(&tdo, d_out, rows, HD, HD, 64, 128);
+  if (rc) return rc;
+  {
+    const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(d_out) + (size_t)T * HD;
+    uint64_t dims[4] = {(uint64_t)HD, (uint64_t)F, (uint64_t)F, (uint64_t)B};
+    uint64_t strides[3] = {(uint64_t)HD * 2, (uint64_t)HD * 2 * F, (uint64_t)HD * 2 * seq};
+    uint32_t box[4] = {64, 1, (uint32_t)F, 1};
+    rc = make_tmap_bf16_nd(&tdocol, base, 4, dims, strides, box);
+    if (rc) return rc;
+  }
+  rc = launch_bwd<ATT_TEXT>(tq, tqcol, tdo, tdocol, a, g.n_text_blocks, st);
+  if (rc) return rc;
+  switch (mode) {
+    case ATT_ROW: rc = launch_bwd<ATT_ROW>(tq, tqcol, tdo, tdocol, a, g.n_img_blocks, st); break;
+    case ATT_COL: rc = launch_bwd<ATT_COL>(tq, tqcol, tdo, tdocol, a, g.n_img_blocks, st); break;
+    case ATT_CONV: rc = launch_bwd<ATT_CONV>(tq, tqcol, tdo, tdocol, a, g.n_img_blocks, st); break;
+    default: return -31;
+  }
+  if (rc) return rc;
+  const int rows_per_sample = (mode == ATT_CONV) ? seq : T;
+  const long long total = static_cast<long long>(B) * rows_per_sample * HD;
+  const int threads = 256;
+  long long blocks = (total + threads - 1) / threads;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  attn_bwd_finish_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(
+      kv_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), a.rot, B, seq, rows_per_sample, HD);
+  return cudaGetLastError() == cudaSuccess ? 0 : -23;
+}

@@ -95,6 +95,7 @@ _f = ctypes.c_float
 class _Sigs:
     b200_gemm_bf16 = [ctypes.POINTER(B200Gemm), _p]
     b200_attn_fwd = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
+    b200_attn_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _i, _i, _i, _i, _p]
 
 
 def check(rc: int, what: str):

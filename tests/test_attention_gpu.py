@@ -32,3 +32,33 @@ def test_attn_fwd(cfg_name, attn_type):
     err = (out.float() - ref_o).abs().max().item()
     assert err < 2e-2, f"o err {err}"
     assert (lse - ref_l).abs().max().item() < 2e-2
+
+
+@pytest.mark.parametrize("cfg_name", ["small", "ttt"])
+@pytest.mark.parametrize("attn_type", ["axial_row", "axial_col", "conv_like"])
+def test_attn_bwd(cfg_name, attn_type):
+    from dalle_b200.models.rotary import rotary_pair_table
+
+    cfg = small_config() if cfg_name == "small" else ttt_config()
+    B = 2
+    M = B * cfg.seq_len
+    qkv = _qkv(cfg, B, seed=1)
+    rot = rotary_pair_table(cfg).cuda()
+    out = torch.zeros(M, cfg.inner_dim, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(B, cfg.heads, cfg.seq_len, device="cuda")
+    A.attn_fwd(qkv, out, lse, cfg, attn_type)
+    d_out = torch.zeros(M + 128, cfg.inner_dim, device="cuda", dtype=torch.bfloat16)
+    d_out[:M] = torch.randn(M, cfg.inner_dim, device="cuda").to(torch.bfloat16)
+    delta = torch.zeros(B, cfg.heads, cfg.seq_len, device="cuda")
+    dqkv = torch.full((M, 3 * cfg.inner_dim), float("nan"), device="cuda", dtype=torch.bfloat16)
+    kv_acc = torch.zeros(M, 2 * cfg.inner_dim, device="cuda")
+    A.attn_bwd(qkv, out, d_out, lse, delta, dqkv, kv_acc, rot, cfg, attn_type)
+    torch.cuda.synchronize()
+    ref = A.attn_bwd_ref(qkv, d_out, cfg, attn_type, rot, cfg.dim_head ** -0.5)
+    assert torch.isfinite(dqkv.float()).all()
+    assert kv_acc.abs().max().item() == 0.0
+    for name, sl in (("dq", slice(0, cfg.inner_dim)), ("dk", slice(cfg.inner_dim, 2 * cfg.inner_dim)),
+                     ("dv", slice(2 * cfg.inner_dim, 3 * cfg.inner_dim))):
+        err = (dqkv[:, sl].float() - ref[:, sl]).abs().max().item()
+        den = ref[:, sl].abs().max().item()
+        assert err / den < 3e-2, f"{name}: err {err} / {den}"
