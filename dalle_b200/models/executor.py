@@ -1,0 +1,328 @@
+"""Reversible layer executor: the product forward/backward of the DALL-E stack.
+
+The reference reaches this through dalle-pytorch's ``ReversibleSequence`` / ``_ReversibleFunction``:
+Python autograd.Functions re-running eager blocks.  Here ONE autograd.Function spans embedding -> 64 reversible
+layers -> final norm -> segment logits -> weighted cross-entropy, and both directions are explicit kernel sequences
+over preallocated buffers:
+
+* residual streams X1, X2 live in fp32 and are updated IN PLACE by the GEMM epilogues
+  (``y = x + scale * (acc + bias)`` forward, ``x = y - scale * (acc + bias)`` when reconstructing), so activation
+  memory is O(1) in depth exactly like the RevNet formulation;
+* GEMM operands are bf16; weights have bf16 shadows refreshed when the fp32 masters change;
+* parameter gradients are accumulated straight into the fp32 ``.grad`` buffers (the collaborative optimizer's
+  ``reuse_grad_buffers=True`` contract, reference arguments.py:75-78) - wgrad GEMMs ``red.add`` into them;
+* logits are never materialised for the full vocabulary: text rows only meet the text segment of the tied matrix,
+  image rows only the image segment (that IS the reference's logits mask), in row chunks.
+
+All math goes through ``dalle_b200.ops``: CUDA kernels for GPU tensors, the PyTorch oracle for CPU tensors, so the
+hand-written backward below is verified against plain autograd on CPU (tests/test_executor.py).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional
+
+import torch
+
+from ..ops import attention as A
+from ..ops import elementwise as E
+from ..ops import gemm as G
+
+
+class _Buffers:
+    pass
+
+
+class Engine:
+    LOGIT_CHUNK_BYTES = 384 << 20
+
+    def __init__(self, model):
+        self.model = model
+        self.cfg = model.cfg
+        self._bufs: Dict[tuple, _Buffers] = {}
+        self._shadow: Dict[int, torch.Tensor] = {}
+        self._shadow_version: Dict[int, int] = {}
+        assert self.cfg.reversible and self.cfg.rotary_emb and self.cfg.shift_tokens, \
+            "the fused executor implements the reference configuration (reversible + rotary + token shift)"
+
+    # ------------------------------------------------------------------------------------------
+    # weights
+    # ------------------------------------------------------------------------------------------
+    def params_changed(self):
+        self._shadow_version.clear()
+
+    def act_dtype(self, device) -> torch.dtype:
+        return torch.bfloat16 if device.type == "cuda" else torch.float32
+
+    def w(self, p: torch.Tensor) -> torch.Tensor:
+        """bf16 shadow (GPU) of a GEMM weight, refreshed when the master's version counter moved."""
+        if p.device.type != "cuda":
+            return p.detach()
+        key = id(p)
+        sh = self._shadow.get(key)
+        if sh is None or sh.shape != p.shape or sh.device != p.device:
+            sh = torch.empty(p.shape, device=p.device, dtype=torch.bfloat16)
+            self._shadow[key] = sh
+            self._shadow_version.pop(key, None)
+        if self._shadow_version.get(key) != p._version:
+            E.cast_bf16(p.detach(), sh)
+            self._shadow_version[key] = p._version
+        return sh
+
+    @staticmethod
+    def grad_of(p: torch.Tensor) -> torch.Tensor:
+        if p.grad is None:
+            p.grad = torch.zeros_like(p, dtype=torch.float32)
+        return p.grad
+
+    # ------------------------------------------------------------------------------------------
+    # workspaces
+    # ------------------------------------------------------------------------------------------
+    def buffers(self, B: int, device, train: bool) -> _Buffers:
+        key = (B, str(device), train)
+        bufs = self._bufs.get(key)
+        if bufs is not None:
+            return bufs
+        cfg = self.cfg
+        M, D, I = B * cfg.seq_len, cfg.dim, cfg.inner_dim
+        hid = D * cfg.ff_mult
+        ad = self.act_dtype(device)
+        pad = 128  # padding rows: the image grid has one position more than tokens (see ops/attention.py)
+
+        def z(*shape, dtype=ad):
+            return torch.zeros(*shape, device=device, dtype=dtype)
+
+        b = _Buffers()
+        b.x1, b.x2 = z(M, D, dtype=torch.float32), z(M, D, dtype=torch.float32)
+        b.h = z(M, D)
+        b.qkv = z(M + pad, 3 * I)
+        b.ao = z(M, I)
+        b.lse = z(B, cfg.heads, cfg.seq_len, dtype=torch.float32)
+        b.u = z(M, hid)
+        b.mean, b.rstd = z(M, dtype=torch.float32), z(M, dtype=torch.float32)
+        b.hf = z(M, D)
+        b.fmean, b.frstd = z(M, dtype=torch.float32), z(M, dtype=torch.float32)
+        b.loss = z(1, dtype=torch.float32)
+        n_text_rows, n_img_rows = B * cfg.text_seq_len, B * cfg.image_seq_len
+        ld_t = (cfg.total_text_tokens + 63) // 64 * 64
+        ld_i = (cfg.num_image_tokens + 63) // 64 * 64
+        rows_t = max(128, min(n_text_rows, self.LOGIT_CHUNK_BYTES // (2 * ld_t) // 128 * 128))
+        rows_i = max(128, min(n_img_rows, self.LOGIT_CHUNK_BYTES // (2 * ld_i) // 128 * 128))
+        b.chunk_t, b.chunk_i, b.ld_t, b.ld_i = rows_t, rows_i, ld_t, ld_i
+        b.logits = z(max(rows_t * ld_t, rows_i * ld_i))
+        if train:
+            b.dx1, b.dx2 = z(M, D, dtype=torch.float32), z(M, D, dtype=torch.float32)
+            b.pre = z(M, 2 * hid)
+            b.dpre = z(M, 2 * hid)
+            b.o = z(M, D)
+            b.d_o = z(M, D)
+            b.dao = z(M + pad, I)
+            b.dqkv = z(M, 3 * I)
+            b.dh = z(M, D)
+            b.delta = z(B, cfg.heads, cfg.seq_len, dtype=torch.float32)
+            b.kv_acc = z(M, 2 * I, dtype=torch.float32)
+            b.dhf = z(M, D)
+        self._bufs[key] = b
+        return b
+
+    # ------------------------------------------------------------------------------------------
+    # token ids
+    # ------------------------------------------------------------------------------------------
+    def token_ids(self, text: torch.Tensor, image: Optional[torch.Tensor]):
+        cfg = self.cfg
+        text = text[:, : cfg.text_seq_len]
+        pad_ids = torch.arange(cfg.text_seq_len, device=text.device) + cfg.num_text_tokens
+        text = torch.where(text == 0, pad_ids, text)
+        text_b = torch.nn.functional.pad(text, (1, 0), value=0)
+        ids = text_b
+        if image is not None and image.numel() > 0:
+            ids = torch.cat((text_b, image + cfg.total_text_tokens), dim=1)
+        ids = ids[:, : cfg.seq_len].contiguous()
+        return ids, text_b[:, 1:].contiguous()
+
+    # ------------------------------------------------------------------------------------------
+    # layer pieces
+    # ------------------------------------------------------------------------------------------
+    def _f_forward(self, i, b, src, dst, alpha, save_o=False):
+        """dst <- dst + alpha * scale_f[i] * attn(shift(LN(src)))   (in place on dst)"""
+        m, cfg = self.model, self.cfg
+        a = m.attn_index[i]
+        M = src.shape[0]
+        E.ln_shift_fwd(src, None, m.norm_f_w[i], m.norm_f_b[i], b.h, b.mean, b.rstd, cfg, True)
+        G.gemm(G.NT, G.EPI_ROTARY, b.h, self.w(m.attn_qkv_w[a]), b.qkv[:M], rot=m.rotary_pairs, seq_len=cfg.seq_len,
+               q_cols=cfg.inner_dim, q_scale=cfg.dim_head ** -0.5)
+        A.attn_fwd(b.qkv, b.ao, b.lse, cfg, cfg.attn_types[i])
+        G.gemm(G.NT, G.EPI_RESID, b.ao, self.w(m.attn_out_w[a]), dst, out2=b.o if save_o else None,
+               bias=m.attn_out_b[a], scale=m.scale_f[i].view(-1), res=dst, alpha=alpha)
+
+    def _g_forward(self, i, b, src, dst, alpha, save=False):
+        """dst <- dst + alpha * scale_g[i] * ff(shift(LN(src)))"""
+        m, cfg = self.model, self.cfg
+        f = m.ff_index[i]
+        hid = cfg.dim * cfg.ff_mult
+        E.ln_shift_fwd(src, None, m.norm_g_w[i], m.norm_g_b[i], b.h, b.mean, b.rstd, cfg, True)
+        G.gemm(G.NT, G.EPI_GEGLU, b.h, self.w(m.ff_w1[f]), b.u, out2=b.pre if save else None, bias=m.ff_b1[f],
+               n_half=hid)
+        G.gemm(G.NT, G.EPI_RESID, b.u, self.w(m.ff_w2[f]), dst, out2=b.o if save else None, bias=m.ff_b2[f],
+               scale=m.scale_g[i].view(-1), res=dst, alpha=alpha)
+
+    def run_stack(self, ids: torch.Tensor, b: _Buffers):
+        cfg = self.cfg
+        E.embed_fwd(ids.view(-1), self.model.emb_weight.detach(), b.x1, b.x2)
+        for i in range(cfg.depth):
+            self._f_forward(i, b, b.x2, b.x1, 1.0)
+            self._g_forward(i, b, b.x1, b.x2, 1.0)
+
+    # ------------------------------------------------------------------------------------------
+    # head: final norm + segment logits + weighted CE
+    # ------------------------------------------------------------------------------------------
+    def _segments(self, B: int, b: _Buffers):
+        cfg = self.cfg
+        nt, ni = B * cfg.text_seq_len, B * cfg.image_seq_len
+        wt = 1.0 / ((cfg.loss_img_weight + 1) * nt)
+        wi = cfg.loss_img_weight / ((cfg.loss_img_weight + 1) * ni)
+        # (row0, rows, vocab0, vocab, ld, chunk, row_weight)
+        return ((0, nt, 0, cfg.total_text_tokens, b.ld_t, b.chunk_t, wt),
+                (nt, ni, cfg.total_text_tokens, cfg.num_image_tokens, b.ld_i, b.chunk_i, wi))
+
+    def _head(self, B, b, labels_t, labels_i, grad_scale: Optional[torch.Tensor]):
+        """Loss (grad_scale None) or loss-gradient pass (writes b.dhf and accumulates the tied-matrix grads)."""
+        m, cfg = self.model, self.cfg
+        W = self.w(m.emb_weight)
+        bias = m.emb_bias.detach()
+        train = grad_scale is not None
+        if train:
+            gW, gb = self.grad_of(m.emb_weight), self.grad_of(m.emb_bias)
+        for (row0, rows, v0, nv, ld, chunk, rw), labels in zip(self._segments(B, b), (labels_t, labels_i)):
+            Wseg = W[v0:v0 + nv]
+            for r0 in range(0, rows, chunk):
+                r = min(chunk, rows - r0)
+                lg = b.logits[: r * ld].view(r, ld)
+                hrows = b.hf[row0 + r0: row0 + r0 + r]
+                G.gemm(G.NT, G.EPI_BF16, hrows, Wseg, lg[:, :nv], bias=bias[v0:v0 + nv])
+                E.ce_fwd_bwd(lg, labels[r0:r0 + r], nv, rw, grad_scale, b.loss, write_grad=train)
+                if train:
+                    dl = lg[:, :nv]
+                    G.gemm(G.NN, G.EPI_BF16, dl, Wseg, b.dhf[row0 + r0: row0 + r0 + r])
+                    G.gemm(G.TN, G.EPI_ATOMIC_F32, dl, hrows, gW[v0:v0 + nv])
+                    E.colsum(dl, gb[v0:v0 + nv])
+
+    def final_norm(self, b):
+        m, cfg = self.model, self.cfg
+        E.ln_shift_fwd(b.x1, b.x2, m.final_norm_w, m.final_norm_b, b.hf, b.fmean, b.frstd, cfg, False,
+                       row_split=cfg.text_seq_len)
+
+    # ------------------------------------------------------------------------------------------
+    # backward of one layer (reconstructs the inputs in place)
+    # ------------------------------------------------------------------------------------------
+    def _g_backward(self, i, b):
+        """y2 = x2 + sg*ff(..y1..):  X2 <- x2 ; dX1 += d ff / d y1 ; param grads."""
+        m, cfg = self.model, self.cfg
+        f = m.ff_index[i]
+        hid = cfg.dim * cfg.ff_mult
+        self._g_forward(i, b, b.x1, b.x2, -1.0, save=True)          # recompute + reconstruct x2 in place
+        sg = m.scale_g[i]
+        E.resid_bwd_prep(b.dx2, b.o, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, b.u, self.grad_of(m.ff_w2[f]))
+        G.gemm(G.NN, G.EPI_GEGLU_BWD, b.d_o, self.w(m.ff_w2[f]), b.dpre, aux=b.pre, n_half=hid)
+        E.colsum(b.dpre, self.grad_of(m.ff_b1[f]))
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dpre, b.h, self.grad_of(m.ff_w1[f]))
+        G.gemm(G.NN, G.EPI_BF16, b.dpre, self.w(m.ff_w1[f]), b.dh)
+        E.ln_shift_bwd(b.dh, b.x1, None, b.mean, b.rstd, m.norm_g_w[i], b.dx1, None, self.grad_of(m.norm_g_w[i]),
+                       self.grad_of(m.norm_g_b[i]), cfg, True, 0)
+
+    def _f_backward(self, i, b):
+        """y1 = x1 + sf*attn(..x2..):  X1 <- x1 ; dX2 += d attn / d x2 ; param grads."""
+        m, cfg = self.model, self.cfg
+        a = m.attn_index[i]
+        M = b.x1.shape[0]
+        self._f_forward(i, b, b.x2, b.x1, -1.0, save_o=True)
+        sf = m.scale_f[i]
+        E.resid_bwd_prep(b.dx1, b.o, sf.view(-1), b.d_o, self.grad_of(sf).view(-1), self.grad_of(m.attn_out_b[a]))
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, b.ao, self.grad_of(m.attn_out_w[a]))
+        G.gemm(G.NN, G.EPI_BF16, b.d_o, self.w(m.attn_out_w[a]), b.dao[:M])
+        A.attn_bwd(b.qkv, b.ao, b.dao, b.lse, b.delta, b.dqkv, b.kv_acc, m.rotary_pairs, cfg, cfg.attn_types[i])
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dqkv, b.h, self.grad_of(m.attn_qkv_w[a]))
+        G.gemm(G.NN, G.EPI_BF16, b.dqkv, self.w(m.attn_qkv_w[a]), b.dh)
+        E.ln_shift_bwd(b.dh, b.x2, None, b.mean, b.rstd, m.norm_f_w[i], b.dx2, None, self.grad_of(m.norm_f_w[i]),
+                       self.grad_of(m.norm_f_b[i]), cfg, True, 0)
+
+    # ------------------------------------------------------------------------------------------
+    # public entry points
+    # ------------------------------------------------------------------------------------------
+    def forward(self, text, image=None, return_loss=False):
+        cfg = self.cfg
+        if not return_loss:
+            return self.forward_logits(text, image)
+        assert image is not None and image.shape[1] == cfg.image_seq_len, "training needs the full image sequence"
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.model.parameters()):
+            anchor = self.model.final_norm_w  # any parameter: makes autograd call our backward
+            return _TrainStep.apply(anchor, self, text, image)
+        return self._loss_forward(text, image, train=False)[0]
+
+    def _loss_forward(self, text, image, train: bool):
+        B, dev = text.shape[0], text.device
+        b = self.buffers(B, dev, train)
+        ids, labels_t = self.token_ids(text, image)
+        self.run_stack(ids, b)
+        self.final_norm(b)
+        b.loss.zero_()
+        self._head(B, b, labels_t.view(-1), image.reshape(-1), None)
+        return b.loss[0].clone(), ids, labels_t
+
+    def _backward(self, B, b, ids, labels_t, image, grad_out: torch.Tensor):
+        m, cfg = self.model, self.cfg
+        scratch_loss = b.loss.clone()
+        gs = grad_out.detach().reshape(1).to(torch.float32)
+        self._head(B, b, labels_t.view(-1), image.reshape(-1), gs)
+        b.loss.copy_(scratch_loss)
+        E.ln_shift_bwd(b.dhf, b.x1, b.x2, b.fmean, b.frstd, m.final_norm_w, b.dx1, b.dx2,
+                       self.grad_of(m.final_norm_w), self.grad_of(m.final_norm_b), cfg, False, 1,
+                       row_split=cfg.text_seq_len)
+        for i in reversed(range(cfg.depth)):
+            self._g_backward(i, b)
+            self._f_backward(i, b)
+        E.embed_bwd(ids.view(-1), b.dx1, b.dx2, self.grad_of(m.emb_weight))
+
+    @torch.no_grad()
+    def forward_logits(self, text, image=None):
+        """Full masked logits [B, n, total_tokens] (API parity with DALLE.forward(return_loss=False))."""
+        from . import reference
+
+        cfg = self.cfg
+        n_img = 0 if image is None else image.shape[1]
+        if text.shape[1] + n_img < cfg.seq_len:
+            # partial sequences (sampling without cache) go through the oracle path
+            return reference.forward(self.model, text, image, False, "dense",
+                                     torch.bfloat16 if text.is_cuda else None)
+        B, dev = text.shape[0], text.device
+        b = self.buffers(B, dev, False)
+        ids, _ = self.token_ids(text, image)
+        self.run_stack(ids, b)
+        m = self.model
+        E.ln_shift_fwd(b.x1, b.x2, m.final_norm_w, m.final_norm_b, b.hf, b.fmean, b.frstd, cfg, False)
+        V = cfg.total_tokens
+        ld = (V + 63) // 64 * 64
+        out = torch.empty(B * cfg.seq_len, ld, device=dev, dtype=self.act_dtype(dev))
+        G.gemm(G.NT, G.EPI_BF16, b.hf, self.w(m.emb_weight), out[:, :V], bias=m.emb_bias.detach())
+        logits = out[:, :V].reshape(B, cfg.seq_len, V).float()
+        return logits.masked_fill(reference.logits_mask(cfg, cfg.seq_len, dev), -torch.finfo(torch.float32).max)
+
+
+class _TrainStep(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, anchor, engine: Engine, text, image):
+        with torch.no_grad():
+            loss, ids, labels_t = engine._loss_forward(text, image, train=True)
+        ctx.engine, ctx.ids, ctx.labels_t, ctx.image = engine, ids, labels_t, image
+        ctx.B, ctx.dev = text.shape[0], text.device
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        eng = ctx.engine
+        b = eng.buffers(ctx.B, ctx.dev, True)
+        with torch.no_grad():
+            eng._backward(ctx.B, b, ctx.ids, ctx.labels_t, ctx.image, grad_out)
+        # parameter gradients were accumulated in place (reuse_grad_buffers contract); nothing flows to `anchor`
+        return None, None, None, None

@@ -41,7 +41,7 @@ def attn_fwd(qkv: torch.Tensor, out: torch.Tensor, lse: torch.Tensor, cfg: Dalle
     """qkv must own at least one padding row beyond B*seq rows when it lives on the GPU (the image grid has one
     position more than there are tokens; the column-gather TMA map touches it)."""
     if not qkv.is_cuda:
-        o, l = attn_core_ref(qkv, cfg, attn_type)
+        o, l = attn_core_ref(qkv[: out.shape[0]], cfg, attn_type)
         out.copy_(o.to(out.dtype))
         lse.copy_(l)
         return out
@@ -69,7 +69,7 @@ def inv_rotary_scale(d_rot: torch.Tensor, rot_pairs: torch.Tensor, cfg: DalleCon
 
 
 def attn_bwd_ref(qkv, d_out, cfg: DalleConfig, attn_type: str, rot_pairs, q_scale):
-    M = d_out.shape[0]
+    M = d_out.shape[0] // cfg.seq_len * cfg.seq_len  # padding rows (fewer than one sample) are ignored
     x = qkv[:M].detach().float().requires_grad_(True)
     with torch.enable_grad():
         o, _ = attn_core_ref(x, cfg, attn_type)

@@ -95,6 +95,14 @@ _f = ctypes.c_float
 class _Sigs:
     b200_gemm_bf16 = [ctypes.POINTER(B200Gemm), _p]
     b200_attn_fwd = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
+    b200_ln_shift_fwd = [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _f, _p]
+    b200_ln_shift_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p]
+    b200_resid_bwd_prep = [_p, _p, _p, _p, _p, _p, _i, _i, _p]
+    b200_colsum_bf16 = [_p, _l, _p, _i, _i, _f, _p]
+    b200_embed_fwd = [_p, _p, _p, _p, _i, _i, _p]
+    b200_embed_bwd = [_p, _p, _p, _p, _i, _i, _p]
+    b200_ce_fwd_bwd = [_p, _l, _p, _i, _i, _f, _p, _p, _i, _p]
+    b200_cast_f32_bf16 = [_p, _p, _l, _p]
     b200_attn_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _i, _i, _i, _i, _p]
 
 

@@ -70,6 +70,38 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* d_out, const flo
                   float* kv_acc, const void* rot, float q_scale, int B, int H, int seq, int T, int F, int mode,
                   int conv_kernel, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Memory-bound kernels (elementwise.cu).  fp32 residual streams, bf16 GEMM operands.
+ * ---------------------------------------------------------------------------------------------- */
+/* row_split > 0 stores the bf16 side as [first row_split tokens of every sample | the remaining tokens] so that the
+ * text / image vocabulary segments of the logits GEMM see contiguous rows.
+ * out(bf16)[t] = token_shift(LayerNorm(x (or 0.5*(x+x2)))) ; also writes per-row mean / rstd (fp32 [M]).
+ * Replaces PreNorm + PreShiftToken of dalle-pytorch. shift=0 gives a plain LayerNorm. */
+int b200_ln_shift_fwd(const float* x, const float* x2, const float* w, const float* b, void* out, float* mean,
+                      float* rstd, int M, int D, int seq, int T, int F, int shift, int row_split, float eps,
+                      void* stream);
+/* Backward of the above. mode 0: dx += grad ; mode 1: dx = dx2 = 0.5*grad (final norm over the stream mean).
+ * dw/db (fp32 [D]) are accumulated into. */
+int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2, const float* mean, const float* rstd,
+                      const float* w, float* dx, float* dx2, float* dw, float* db, int M, int D, int seq, int T, int F,
+                      int shift, int row_split, int mode, void* stream);
+/* LayerScale/residual backward prep: d_o(bf16) = dy*scale ; dscale += colsum(dy*o) ; dbias += colsum(dy*scale). */
+int b200_resid_bwd_prep(const float* dy, const void* o, const float* scale, void* d_o, float* dscale, float* dbias,
+                        int M, int D, void* stream);
+/* out[col] += alpha * sum over rows of x (bf16 [M, N], leading dimension ld). */
+int b200_colsum_bf16(const void* x, long long ld, float* out, int M, int N, float alpha, void* stream);
+/* Tied embedding (dalle-pytorch SharedEmbedding): gather rows of W (fp32) into one or two fp32 streams /
+ * scatter-add (d1 + d2) back into dW. */
+int b200_embed_fwd(const long long* ids, const float* W, float* x1, float* x2, int M, int D, void* stream);
+int b200_embed_bwd(const long long* ids, const float* d1, const float* d2, float* dW, int M, int D, void* stream);
+/* Cross-entropy over one vocabulary segment, in place: logits(bf16 [rows, ld]) -> dlogits ; loss_acc += weighted
+ * NLL.  The logits mask of the reference (text positions predict text ids only, image positions image ids only,
+ * SURVEY M1) is realised by running the segment GEMMs separately, so only n_classes columns exist. */
+int b200_ce_fwd_bwd(void* logits, long long ld, const long long* labels, int rows, int n_classes, float row_weight,
+                    const float* grad_scale /* device scalar or NULL = 1 */, float* loss_acc, int write_grad,
+                    void* stream);
+int b200_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
