@@ -58,6 +58,12 @@ class Engine:
         """bf16 shadow (GPU) of a GEMM weight, refreshed when the master's version counter moved."""
         if p.device.type != "cuda":
             return p.detach()
+        flat_shadow = getattr(p, "_bf16_shadow", None)
+        if flat_shadow is not None:  # maintained by the fused optimizer (optim/lamb8bit.py)
+            if getattr(p, "_shadow_version", None) != p._version:
+                E.cast_bf16(p.detach(), flat_shadow)
+                p._shadow_version = p._version
+            return flat_shadow
         key = id(p)
         sh = self._shadow.get(key)
         if sh is None or sh.shape != p.shape or sh.device != p.device:
@@ -72,7 +78,15 @@ class Engine:
     @staticmethod
     def grad_of(p: torch.Tensor) -> torch.Tensor:
         if p.grad is None:
-            p.grad = torch.zeros_like(p, dtype=torch.float32)
+            layout = getattr(p, "_flat_layout", None)
+            if layout is not None:  # re-attach the view into the flat gradient buffer
+                i = next(k for k, q in enumerate(layout.params) if q is p)
+                o = layout.offsets[i]
+                view = layout.flat_grad[o:o + p.numel()].view(p.shape)
+                view.zero_()
+                p.grad = view
+            else:
+                p.grad = torch.zeros_like(p, dtype=torch.float32)
         return p.grad
 
     # ------------------------------------------------------------------------------------------

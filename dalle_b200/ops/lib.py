@@ -103,6 +103,8 @@ class _Sigs:
     b200_embed_bwd = [_p, _p, _p, _p, _i, _i, _p]
     b200_ce_fwd_bwd = [_p, _l, _p, _i, _i, _f, _p, _p, _i, _p]
     b200_cast_f32_bf16 = [_p, _p, _l, _p]
+    b200_lamb_step = [_p, _p, _p, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _i, _p, _p,
+                      _f, _f, _f, _f, _f, _f, _f, _i, _p]
     b200_attn_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _i, _i, _i, _i, _p]
 
 

@@ -102,6 +102,20 @@ int b200_ce_fwd_bwd(void* logits, long long ld, const long long* labels, int row
                     void* stream);
 int b200_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Fused LAMB with block-wise 8-bit moments over one flat fp32 parameter buffer (lamb.cu).
+ * Replaces reference lib/training/lamb_8bit.py (CPULAMB8Bit.step) + bitsandbytes quantize/dequantize_blockwise.
+ * blocks: one 24-byte record {int tensor, int valid, long long state_off, int quantized, int absmax_idx} per
+ * 4096-element block.  tensor_sums [2*n_tensors], trust_out [3*n_tensors] (weight_norm, step_norm, trust),
+ * stats [2] = {sum g^2, non-finite flag}: all device scratch owned by the caller.
+ * If a non-finite gradient is seen the parameters are left untouched and stats[1] = 1.
+ * ---------------------------------------------------------------------------------------------- */
+int b200_lamb_step(float* grad, float* param, void* param_bf16, long long n_padded, void* q1, void* q2, float* f1,
+                   float* f2, float* absmax1, float* absmax2, const float* code1, const float* code2,
+                   const void* blocks, int n_blocks, const float* wd_per_tensor, float* tensor_sums, int n_tensors,
+                   float* trust_out, float* stats, float beta1, float beta2, float eps, float max_grad_norm,
+                   float clamp_value, float lr, float grad_scale, int zero_grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
