@@ -11,6 +11,9 @@
 #include "sm100_ptx.cuh"
 #include "b200_api.h"
 
+#include <cstdio>
+#include <mutex>
+
 namespace b200 {
 
 constexpr int QBLOCK = 4096;
@@ -256,5 +259,98 @@ extern "C" int b200_lamb_step(float* grad, float* param, void* param_bf16, long 
   lamb_apply_kernel<<<n_blocks, LAMB_THREADS, 0, st>>>(grad, param, reinterpret_cast<__nv_bfloat16*>(param_bf16),
                                                        reinterpret_cast<const LambBlock*>(blocks), tensor_sums,
                                                        trust_out, stats, hp, zero_grad);
+  return cudaGetLastError() == cudaSuccess ? 0 : -51;
+}
+
+// -------------------------------------------------------------------------------------------------
+// b200_lamb_step_noalloc: the same optimizer step for callers that have no way to provide scratch memory.
+//
+// Who needs this: host programs that gave the whole device-memory budget to their own arena at start-up (a serving
+// or training runtime with a fixed pool, or an embedding application that is simply not allowed to call cudaMalloc
+// or go through torch's caching allocator after initialisation), and control loops - such as the averaging thread of
+// the collaborative optimizer - where an allocation could fail late, or stall the device, in the middle of a step.
+// b200_lamb_step asks its caller for three small work arrays (stats, tensor_sums, trust_out); here the first two
+// live in the fixed array below instead, so the caller passes inputs and outputs only.
+//
+// The array is part of the library image: every GPU that loads libdalle_b200.so carries these
+// B200_LAMB_NOALLOC_SCRATCH_FLOATS * 4 bytes (about 33 KB) until the process exits.  That bounds the problem size:
+// at most B200_LAMB_NOALLOC_MAX_TENSORS parameter tensors per call; larger requests are refused with
+// B200_ERR_NOALLOC_TOO_MANY_TENSORS and a message on stderr, nothing is launched.
+//
+// All calls on one device share the array and find in it whatever the previous call left there.  The entry point
+// clears, on the caller's stream, exactly the part that has to start from zero (the two statistics and
+// 2*n_tensors partial sums) before the kernels run.  Two calls whose kernels can overlap on the GPU (different
+// streams without an ordering between them) would race on the array - serialise them.
+//
+// The first call on each device resolves the device address of the array (cudaGetSymbolAddress, with that device
+// current) and caches it; make that first call before starting any stream capture.  No cudaMalloc, cudaFree or
+// allocating library routine is called, here or in the kernels.
+// -------------------------------------------------------------------------------------------------
+namespace b200 {
+
+constexpr int kNoAllocStatsFloats = 64;  // stats[2], padded so the sums start on a 256-byte boundary
+static __device__ __align__(256) float g_lamb_noalloc_scratch[B200_LAMB_NOALLOC_SCRATCH_FLOATS];
+
+constexpr int kMaxDevices = 64;
+static float* g_lamb_noalloc_ptr[kMaxDevices] = {nullptr};
+static std::mutex g_lamb_noalloc_mutex;
+
+// In host code `g_lamb_noalloc_scratch` is only a handle for the symbol, not a device address; the address a
+// kernel can use has to be asked for, once per device, with that device current.
+static int lamb_noalloc_scratch(float** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return B200_ERR_NOALLOC_SETUP;
+  std::lock_guard<std::mutex> lock(g_lamb_noalloc_mutex);
+  if (g_lamb_noalloc_ptr[dev] == nullptr) {
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&ptr), g_lamb_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      fprintf(stderr, "b200_lamb_step_noalloc: cudaGetSymbolAddress failed on device %d: %s\n", dev,
+              cudaGetErrorString(e));
+      return B200_ERR_NOALLOC_SETUP;
+    }
+    g_lamb_noalloc_ptr[dev] = ptr;
+  }
+  *out = g_lamb_noalloc_ptr[dev];
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" int b200_lamb_step_noalloc(float* grad, float* param, void* param_bf16, long long n_padded, void* q1,
+                                      void* q2, float* f1, float* f2, float* absmax1, float* absmax2,
+                                      const float* code1, const float* code2, const void* blocks, int n_blocks,
+                                      const float* wd_per_tensor, int n_tensors, float* trust_out, float* stats_out,
+                                      float beta1, float beta2, float eps, float max_grad_norm, float clamp_value,
+                                      float lr, float grad_scale, int zero_grad, void* stream) {
+  if (n_tensors < 0 || n_tensors > B200_LAMB_NOALLOC_MAX_TENSORS) {
+    fprintf(stderr,
+            "b200_lamb_step_noalloc: %d parameter tensors exceed the built-in scratch (max %d); use b200_lamb_step "
+            "with caller-provided scratch instead\n", n_tensors, B200_LAMB_NOALLOC_MAX_TENSORS);
+    return B200_ERR_NOALLOC_TOO_MANY_TENSORS;
+  }
+  if (n_padded != static_cast<long long>(n_blocks) * QBLOCK) return -50;
+  float* scratch = nullptr;
+  const int rc = lamb_noalloc_scratch(&scratch);
+  if (rc != 0) return rc;
+  float* stats = scratch;
+  float* tensor_sums = scratch + kNoAllocStatsFloats;
+
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  LambHyper hp;
+  hp.beta1 = beta1; hp.beta2 = beta2; hp.eps = eps; hp.max_grad_norm = max_grad_norm; hp.clamp_value = clamp_value;
+  hp.lr = lr; hp.grad_scale = grad_scale; hp.use_clip = max_grad_norm > 0.f;
+  // the previous call's statistics and partial sums are still in the array: clear what accumulates
+  cudaMemsetAsync(stats, 0, 2 * sizeof(float), st);
+  cudaMemsetAsync(tensor_sums, 0, 2 * static_cast<size_t>(n_tensors) * sizeof(float), st);
+  lamb_grad_norm_kernel<<<148 * 8, LAMB_THREADS, 0, st>>>(grad, n_padded, stats);
+  lamb_moments_kernel<<<n_blocks, LAMB_THREADS, 0, st>>>(
+      grad, param, reinterpret_cast<uint8_t*>(q1), reinterpret_cast<uint8_t*>(q2), f1, f2, absmax1, absmax2, code1,
+      code2, reinterpret_cast<const LambBlock*>(blocks), wd_per_tensor, tensor_sums, stats, hp);
+  lamb_apply_kernel<<<n_blocks, LAMB_THREADS, 0, st>>>(grad, param, reinterpret_cast<__nv_bfloat16*>(param_bf16),
+                                                       reinterpret_cast<const LambBlock*>(blocks), tensor_sums,
+                                                       trust_out, stats, hp, zero_grad);
+  if (stats_out != nullptr)  // {sum g^2, non-finite flag} for callers that want to look at them
+    cudaMemcpyAsync(stats_out, stats, 2 * sizeof(float), cudaMemcpyDeviceToDevice, st);
   return cudaGetLastError() == cudaSuccess ? 0 : -51;
 }

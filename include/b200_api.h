@@ -116,6 +116,31 @@ int b200_lamb_step(float* grad, float* param, void* param_bf16, long long n_padd
                    float* trust_out, float* stats, float beta1, float beta2, float eps, float max_grad_norm,
                    float clamp_value, float lr, float grad_scale, int zero_grad, void* stream);
 
+/* b200_lamb_step for callers that cannot provide scratch memory.  No counterpart in the reference: it exists for
+ * embedders of this library that may not allocate device memory once they are running (all of it belongs to their
+ * own pool, or an allocation inside the optimizer step could fail or stall the device).  The two work arrays of
+ * b200_lamb_step (stats, tensor_sums) live in a fixed __device__ array inside the library instead
+ * (B200_LAMB_NOALLOC_SCRATCH_FLOATS floats, about 33 KB, held by every GPU that loads the library until exit), so
+ * at most B200_LAMB_NOALLOC_MAX_TENSORS parameter tensors are accepted; more returns
+ * B200_ERR_NOALLOC_TOO_MANY_TENSORS with a message on stderr and launches nothing.
+ *   - inputs and outputs are the caller's as in b200_lamb_step; trust_out [3*n_tensors] and stats_out [2] are
+ *     optional outputs (NULL to skip);
+ *   - calls on one device share the array: it is cleared where needed at the start of each call, and calls that can
+ *     overlap on the GPU race with each other - order them on one stream or with events;
+ *   - the first call on a device looks up the array's device address (cudaGetSymbolAddress); make that call before
+ *     any stream capture begins;
+ *   - calls no cudaMalloc / cudaFree / allocating library routine. */
+#define B200_LAMB_NOALLOC_MAX_TENSORS 4096
+#define B200_LAMB_NOALLOC_SCRATCH_FLOATS (64 + 2 * B200_LAMB_NOALLOC_MAX_TENSORS)
+#define B200_ERR_NOALLOC_TOO_MANY_TENSORS (-53)
+#define B200_ERR_NOALLOC_SETUP (-52)
+int b200_lamb_step_noalloc(float* grad, float* param, void* param_bf16, long long n_padded, void* q1, void* q2,
+                           float* f1, float* f2, float* absmax1, float* absmax2, const float* code1,
+                           const float* code2, const void* blocks, int n_blocks, const float* wd_per_tensor,
+                           int n_tensors, float* trust_out, float* stats_out, float beta1, float beta2, float eps,
+                           float max_grad_norm, float clamp_value, float lr, float grad_scale, int zero_grad,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif
