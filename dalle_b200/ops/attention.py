@@ -10,6 +10,7 @@ import torch
 from ..config import DalleConfig
 from ..models.masks import ATTN_TYPE_CODES, static_mask
 from . import lib
+from .gemm import rot_transposed
 
 _MASK_CACHE = {}
 
@@ -87,7 +88,7 @@ def attn_bwd(qkv, out, d_out, lse, delta, dqkv, kv_acc, rot_pairs, cfg: DalleCon
     B = out.shape[0] // cfg.seq_len
     rc = lib.cuda_lib().b200_attn_bwd(qkv.data_ptr(), out.data_ptr(), d_out.data_ptr(), lse.data_ptr(),
                                       delta.data_ptr(), dqkv.data_ptr(), kv_acc.data_ptr(), rot_pairs.data_ptr(),
-                                      q_scale, B, cfg.heads, cfg.seq_len, cfg.text_len, cfg.image_fmap_size,
+                                      rot_transposed(rot_pairs).data_ptr(), q_scale, B, cfg.heads, cfg.seq_len, cfg.text_len, cfg.image_fmap_size,
                                       ATTN_TYPE_CODES[attn_type] + 1, cfg.conv_kernel_size,
                                       torch.cuda.current_stream().cuda_stream)
     lib.check(rc, "b200_attn_bwd")

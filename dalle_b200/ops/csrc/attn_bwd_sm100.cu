@@ -12,6 +12,8 @@
 #include "attn_common.cuh"
 #include "b200_api.h"
 
+#include <cstdlib>
+
 namespace b200 {
 
 int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols,
@@ -30,7 +32,10 @@ struct AttnBwdArgs {
   __nv_bfloat16* dqkv;  // [B*seq, 3*H*64]
   float* kv_acc;        // [B*seq, 2*H*64] fp32, zero on entry
   const float2* rot;    // [seq+1][32] (cos, sin)
+  const float2* rot_t;  // [32][seq+1] pair-major copy (coalesced for thread-per-row access)
+  int rot_len;
   float q_scale;
+  int debug_skip_atomics;
 };
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -38,10 +43,10 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
 }
 
 // v[0..31] = 32 consecutive head dims starting at d0 (0 or 32) -> inverse rotation by the position's angles
-__device__ __forceinline__ void inv_rotary32(float* v, const float2* rot_row, int d0, float scale) {
+__device__ __forceinline__ void inv_rotary32(float* v, const float2* rot_t_pos, int rot_len, int d0, float scale) {
 #pragma unroll
   for (int j = 0; j < 32; j += 2) {
-    const float2 cs = __ldg(rot_row + ((d0 + j) >> 1));
+    const float2 cs = __ldg(rot_t_pos + static_cast<long long>((d0 + j) >> 1) * rot_len);
     const float x0 = v[j], x1 = v[j + 1];
     v[j] = (x0 * cs.x + x1 * cs.y) * scale;
     v[j + 1] = (x1 * cs.x - x0 * cs.y) * scale;
@@ -317,10 +322,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
         const long long grow = static_cast<long long>(b) * g.seq + ktok;
         if (direct) {
-          inv_rotary32(v, a.rot + static_cast<long long>(ktok) * 32, d0, 1.0f);
+          inv_rotary32(v, a.rot_t + ktok, a.rot_len, d0, 1.0f);
           store32_bf16(a.dqkv + grow * (3 * HD) + (is_v ? 2 : 1) * HD + h * 64 + d0, v);
         } else {
           float* dst = a.kv_acc + grow * (2 * HD) + (is_v ? HD : 0) + h * 64 + d0;
+          if (a.debug_skip_atomics) continue;
 #pragma unroll
           for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
         }
@@ -338,7 +344,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       float v[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      inv_rotary32(v, a.rot + static_cast<long long>(tpos) * 32, half * 32, a.q_scale);
+      inv_rotary32(v, a.rot_t + tpos, a.rot_len, half * 32, a.q_scale);
       store32_bf16(a.dqkv + (static_cast<long long>(b) * g.seq + tpos) * (3 * HD) + h * 64 + half * 32, v);
     }
   }
@@ -351,43 +357,58 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   }
 }
 
-// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]        (one warp per (row, head) pair group)
+// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]        (8 lanes x 16 B per (row, head))
 __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
                                   float* __restrict__ delta, int rows, int H, int seq) {
-  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (gw >= rows * H) return;
-  const int row = gw / H, h = gw - row * H;
-  const long long off = static_cast<long long>(row) * H * 64 + h * 64 + lane * 2;
-  const float2 x = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(o + off));
-  const float2 y = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(d_o + off));
-  const float s = warp_sum(x.x * y.x + x.y * y.y);
-  if (lane == 0) {
-    const int b = row / seq, t = row - b * seq;
-    delta[(static_cast<long long>(b) * H + h) * seq + t] = s;
+  const long long gid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long grp = gid >> 3;  // (row, head)
+  const int sub = static_cast<int>(gid & 7);
+  if (grp >= static_cast<long long>(rows) * H) return;
+  const int row = static_cast<int>(grp / H), h = static_cast<int>(grp - static_cast<long long>(row) * H);
+  const long long off = static_cast<long long>(row) * H * 64 + h * 64 + sub * 8;
+  const uint4 x = *reinterpret_cast<const uint4*>(o + off);
+  const uint4 y = *reinterpret_cast<const uint4*>(d_o + off);
+  float2 a, b;
+  float s = 0.f;
+  a = unpack_bf16x2(x.x); b = unpack_bf16x2(y.x); s += a.x * b.x + a.y * b.y;
+  a = unpack_bf16x2(x.y); b = unpack_bf16x2(y.y); s += a.x * b.x + a.y * b.y;
+  a = unpack_bf16x2(x.z); b = unpack_bf16x2(y.z); s += a.x * b.x + a.y * b.y;
+  a = unpack_bf16x2(x.w); b = unpack_bf16x2(y.w); s += a.x * b.x + a.y * b.y;
+  s += __shfl_xor_sync(0xffffffffu, s, 4);
+  s += __shfl_xor_sync(0xffffffffu, s, 2);
+  s += __shfl_xor_sync(0xffffffffu, s, 1);
+  if (sub == 0) {
+    const int b_ = row / seq, t = row - b_ * seq;
+    delta[(static_cast<long long>(b_) * H + h) * seq + t] = s;
   }
 }
 
 // kv_acc (fp32, rot domain) -> inverse rotary -> bf16 into d_qkv k/v sections; clears kv_acc.
 // rows_per_sample = T (axial: only text keys went through the accumulator) or seq (conv_like).
-__global__ void attn_bwd_finish_kernel(float* __restrict__ kv_acc, __nv_bfloat16* __restrict__ dqkv,
-                                       const float2* __restrict__ rot, int B, int seq, int rows_per_sample, int HD) {
-  const int pairs_per_row = HD;  // (k,v) x HD/2 pairs
-  const long long total = static_cast<long long>(B) * rows_per_sample * pairs_per_row;
-  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
-       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int pr = static_cast<int>(idx % pairs_per_row);
-    const long long rr = idx / pairs_per_row;
-    const int t = static_cast<int>(rr % rows_per_sample), b = static_cast<int>(rr / rows_per_sample);
-    const long long grow = static_cast<long long>(b) * seq + t;
-    const int col = pr * 2;            // column inside [k | v] (2*HD wide)
-    float2* src = reinterpret_cast<float2*>(kv_acc + grow * (2 * HD) + col);
-    const float2 x = *src;
-    *src = make_float2(0.f, 0.f);
-    const float2 cs = __ldg(rot + static_cast<long long>(t) * 32 + ((col & 63) >> 1));
-    const float o0 = x.x * cs.x + x.y * cs.y, o1 = x.y * cs.x - x.x * cs.y;
-    *reinterpret_cast<uint32_t*>(dqkv + grow * (3 * HD) + HD + col) = pack_bf16x2(o0, o1);
-  }
+// thread = 8 consecutive columns (4 rotary pairs) of one row.
+__global__ void __launch_bounds__(256)
+attn_bwd_finish_kernel(float* __restrict__ kv_acc, __nv_bfloat16* __restrict__ dqkv, const float2* __restrict__ rot,
+                       int B, int seq, int rows_per_sample, int HD) {
+  const int groups_per_row = (2 * HD) / 8;
+  const unsigned total = static_cast<unsigned>(B) * rows_per_sample * groups_per_row;
+  const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const unsigned gcol = idx % groups_per_row, rr = idx / groups_per_row;
+  const int t = rr % rows_per_sample, b = rr / rows_per_sample;
+  const long long grow = static_cast<long long>(b) * seq + t;
+  const int col = gcol * 8;
+  float4* src = reinterpret_cast<float4*>(kv_acc + grow * (2 * HD) + col);
+  const float4 a = src[0], c = src[1];
+  src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+  src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4* rt = reinterpret_cast<const float4*>(rot + static_cast<long long>(t) * 32 + ((col & 63) >> 1));
+  const float4 r01 = __ldg(rt), r23 = __ldg(rt + 1);  // (cos0, sin0, cos1, sin1), (cos2, sin2, cos3, sin3)
+  uint4 o;
+  o.x = pack_bf16x2(a.x * r01.x + a.y * r01.y, a.y * r01.x - a.x * r01.y);
+  o.y = pack_bf16x2(a.z * r01.z + a.w * r01.w, a.w * r01.z - a.z * r01.w);
+  o.z = pack_bf16x2(c.x * r23.x + c.y * r23.y, c.y * r23.x - c.x * r23.y);
+  o.w = pack_bf16x2(c.z * r23.z + c.w * r23.w, c.w * r23.z - c.z * r23.w);
+  *reinterpret_cast<uint4*>(dqkv + grow * (3 * HD) + HD + col) = o;
 }
 
 template <int MODE>
@@ -407,7 +428,7 @@ static int launch_bwd(const CUtensorMap& t1, const CUtensorMap& t2, const CUtens
 using namespace b200;
 
 extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
-                             void* dqkv, float* kv_acc, const void* rot, float q_scale, int B, int H, int seq, int T,
+                             void* dqkv, float* kv_acc, const void* rot, const void* rot_t, float q_scale, int B, int H, int seq, int T,
                              int F, int mode, int conv_kernel, void* stream) {
   AttnGeom g;
   g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
@@ -416,9 +437,9 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int HD = H * 64;
   {
-    const long long warps = static_cast<long long>(B) * seq * H;
+    const long long groups = static_cast<long long>(B) * seq * H;
     const int threads = 256;
-    const long long blocks = (warps * 32 + threads - 1) / threads;
+    const long long blocks = (groups * 8 + threads - 1) / threads;
     attn_delta_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B * seq, H,
         seq);
@@ -426,6 +447,8 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   AttnBwdArgs a;
   a.g = g; a.lse = lse; a.delta = delta; a.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv); a.kv_acc = kv_acc;
   a.rot = reinterpret_cast<const float2*>(rot); a.q_scale = q_scale;
+  a.rot_t = reinterpret_cast<const float2*>(rot_t); a.rot_len = seq + 1;
+  a.debug_skip_atomics = getenv("B200_ATTN_SKIP_KV_ATOMICS") != nullptr;
 
   CUtensorMap tq, ttail, tqcol, tdo, tdocol;
   int rc = attn_make_maps(qkv, g, ATT_COL, &tq, &ttail, &tqcol);
@@ -451,10 +474,10 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   }
   if (rc) return rc;
   const int rows_per_sample = (mode == ATT_CONV) ? seq : T;
-  const long long total = static_cast<long long>(B) * rows_per_sample * HD;
+  const long long total = static_cast<long long>(B) * rows_per_sample * (2 * HD / 8);
+  if (total >= (1ll << 32)) return -24;
   const int threads = 256;
-  long long blocks = (total + threads - 1) / threads;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  const long long blocks = (total + threads - 1) / threads;
   attn_bwd_finish_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(
       kv_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), a.rot, B, seq, rows_per_sample, HD);
   return cudaGetLastError() == cudaSuccess ? 0 : -23;

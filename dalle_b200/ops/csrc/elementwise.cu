@@ -115,91 +115,97 @@ __global__ void ln_shift_apply_kernel(const float* __restrict__ x, const float* 
 // transposed shift; dx = rstd * (w*dn - mean(w*dn) - xhat * mean(w*dn*xhat)).
 //   mode 0: dx_out[t] += dx           (reversible block: accumulate into the running stream gradient)
 //   mode 1: dx_out[t] = dx2_out[t] = 0.5 * dx   (final norm over the mean of the two streams)
-// dw += dn * xhat, db += dn reduced over rows (register partials -> smem -> one atomicAdd per column per block).
+// Row kernel (one warp per row, high occupancy) + column kernel for dw += dn*xhat, db += dn.
 __global__ void __launch_bounds__(256)
-ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
-                    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
-                    float* __restrict__ dx_out, float* __restrict__ dx2_out, float* __restrict__ dw,
-                    float* __restrict__ db, int M, int D, ShiftGeom sg, int mode) {
-  extern __shared__ float red[];  // [2][D]
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nwarps = blockDim.x >> 5;
+ln_shift_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
+                       const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
+                       float* __restrict__ dx_out, float* __restrict__ dx2_out, int M, int D, ShiftGeom sg, int mode) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= M) return;
   const int nv = D / 128;
-  float4 aw[MAXV], ab[MAXV];
-#pragma unroll
-  for (int k = 0; k < MAXV; ++k) { aw[k] = make_float4(0.f, 0.f, 0.f, 0.f); ab[k] = make_float4(0.f, 0.f, 0.f, 0.f); }
-
-  for (int row = blockIdx.x * nwarps + warp; row < M; row += gridDim.x * nwarps) {
-    const int bidx = row / sg.seq, t = row - bidx * sg.seq;
-    const float mu = mean[row], rs = rstd[row];
-    float4 dn[MAXV], xh[MAXV];
-    float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-    for (int k = 0; k < MAXV; ++k) {
-      if (k < nv) {
-        const int col = k * 128 + lane * 4;
-        const int dt = shift_dst(sg, t, col, D);
-        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (dt >= 0) {
-          const uint2 u = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
-          const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
-          g = make_float4(a.x, a.y, c.x, c.y);
-        }
-        float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
-        if (x2) {
-          const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
-          v.x = 0.5f * (v.x + u2.x); v.y = 0.5f * (v.y + u2.y); v.z = 0.5f * (v.z + u2.z); v.w = 0.5f * (v.w + u2.w);
-        }
-        const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
-        xh[k] = make_float4((v.x - mu) * rs, (v.y - mu) * rs, (v.z - mu) * rs, (v.w - mu) * rs);
-        aw[k].x += g.x * xh[k].x; aw[k].y += g.y * xh[k].y; aw[k].z += g.z * xh[k].z; aw[k].w += g.w * xh[k].w;
-        ab[k].x += g.x; ab[k].y += g.y; ab[k].z += g.z; ab[k].w += g.w;
-        dn[k] = make_float4(g.x * ww.x, g.y * ww.y, g.z * ww.z, g.w * ww.w);
-        s1 += dn[k].x + dn[k].y + dn[k].z + dn[k].w;
-        s2 += dn[k].x * xh[k].x + dn[k].y * xh[k].y + dn[k].z * xh[k].z + dn[k].w * xh[k].w;
-      }
-    }
-    s1 = warp_sum(s1) / D;
-    s2 = warp_sum(s2) / D;
-#pragma unroll
-    for (int k = 0; k < MAXV; ++k) {
-      if (k < nv) {
-        const int col = k * 128 + lane * 4;
-        float4 d;
-        d.x = rs * (dn[k].x - s1 - xh[k].x * s2);
-        d.y = rs * (dn[k].y - s1 - xh[k].y * s2);
-        d.z = rs * (dn[k].z - s1 - xh[k].z * s2);
-        d.w = rs * (dn[k].w - s1 - xh[k].w * s2);
-        float4* p = reinterpret_cast<float4*>(dx_out + static_cast<long long>(row) * D + col);
-        if (mode == 0) {
-          const float4 o = *p;
-          *p = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w);
-        } else {
-          const float4 hlf = make_float4(0.5f * d.x, 0.5f * d.y, 0.5f * d.z, 0.5f * d.w);
-          *p = hlf;
-          *reinterpret_cast<float4*>(dx2_out + static_cast<long long>(row) * D + col) = hlf;
-        }
-      }
-    }
-  }
-  // block reduction of the column partials
-  for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) red[i] = 0.f;
-  __syncthreads();
+  const int bidx = row / sg.seq, t = row - bidx * sg.seq;
+  const float mu = mean[row], rs = rstd[row];
+  float4 dn[MAXV], xh[MAXV];
+  float s1 = 0.f, s2 = 0.f;
 #pragma unroll
   for (int k = 0; k < MAXV; ++k) {
     if (k < nv) {
       const int col = k * 128 + lane * 4;
-      atomicAdd(&red[col], aw[k].x); atomicAdd(&red[col + 1], aw[k].y);
-      atomicAdd(&red[col + 2], aw[k].z); atomicAdd(&red[col + 3], aw[k].w);
-      atomicAdd(&red[D + col], ab[k].x); atomicAdd(&red[D + col + 1], ab[k].y);
-      atomicAdd(&red[D + col + 2], ab[k].z); atomicAdd(&red[D + col + 3], ab[k].w);
+      const int dt = shift_dst(sg, t, col, D);
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dt >= 0) {
+        const uint2 u = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
+        const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
+        g = make_float4(a.x, a.y, c.x, c.y);
+      }
+      float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
+      if (x2) {
+        const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
+        v.x = 0.5f * (v.x + u2.x); v.y = 0.5f * (v.y + u2.y); v.z = 0.5f * (v.z + u2.z); v.w = 0.5f * (v.w + u2.w);
+      }
+      const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
+      xh[k] = make_float4((v.x - mu) * rs, (v.y - mu) * rs, (v.z - mu) * rs, (v.w - mu) * rs);
+      dn[k] = make_float4(g.x * ww.x, g.y * ww.y, g.z * ww.z, g.w * ww.w);
+      s1 += dn[k].x + dn[k].y + dn[k].z + dn[k].w;
+      s2 += dn[k].x * xh[k].x + dn[k].y * xh[k].y + dn[k].z * xh[k].z + dn[k].w * xh[k].w;
     }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    atomicAdd(&dw[i], red[i]);
-    atomicAdd(&db[i], red[D + i]);
+  s1 = warp_sum(s1) / D;
+  s2 = warp_sum(s2) / D;
+#pragma unroll
+  for (int k = 0; k < MAXV; ++k) {
+    if (k < nv) {
+      const int col = k * 128 + lane * 4;
+      float4 d;
+      d.x = rs * (dn[k].x - s1 - xh[k].x * s2);
+      d.y = rs * (dn[k].y - s1 - xh[k].y * s2);
+      d.z = rs * (dn[k].z - s1 - xh[k].z * s2);
+      d.w = rs * (dn[k].w - s1 - xh[k].w * s2);
+      float4* p = reinterpret_cast<float4*>(dx_out + static_cast<long long>(row) * D + col);
+      if (mode == 0) {
+        const float4 o = *p;
+        *p = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w);
+      } else {
+        const float4 hlf = make_float4(0.5f * d.x, 0.5f * d.y, 0.5f * d.z, 0.5f * d.w);
+        *p = hlf;
+        *reinterpret_cast<float4*>(dx2_out + static_cast<long long>(row) * D + col) = hlf;
+      }
+    }
   }
+}
+
+// dw[col] += sum_rows dn*xhat ; db[col] += sum_rows dn.  thread = 4 columns, block = one row slice.
+__global__ void __launch_bounds__(256)
+ln_shift_bwd_dwdb_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x,
+                         const float* __restrict__ x2, const float* __restrict__ mean, const float* __restrict__ rstd,
+                         float* __restrict__ dw, float* __restrict__ db, int M, int D, ShiftGeom sg) {
+  const int cols_per_block = blockDim.x * 4;
+  const int stripes = D / cols_per_block;
+  const int col = (blockIdx.x % stripes) * cols_per_block + threadIdx.x * 4;
+  const int rsplit = blockIdx.x / stripes, nsplit = gridDim.x / stripes;
+  const int rows_per = (M + nsplit - 1) / nsplit;
+  const int r0 = rsplit * rows_per, r1 = min(M, r0 + rows_per);
+  float4 aw = make_float4(0.f, 0.f, 0.f, 0.f), ab = make_float4(0.f, 0.f, 0.f, 0.f);
+  int bidx = r0 / sg.seq, t = r0 - bidx * sg.seq;
+  for (int row = r0; row < r1; ++row) {
+    const int dt = shift_dst(sg, t, col, D);
+    if (dt >= 0) {
+      const uint2 u = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
+      const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
+      float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
+      if (x2) {
+        const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
+        v.x = 0.5f * (v.x + u2.x); v.y = 0.5f * (v.y + u2.y); v.z = 0.5f * (v.z + u2.z); v.w = 0.5f * (v.w + u2.w);
+      }
+      const float mu = mean[row], rs = rstd[row];
+      aw.x += a.x * (v.x - mu) * rs; aw.y += a.y * (v.y - mu) * rs;
+      aw.z += c.x * (v.z - mu) * rs; aw.w += c.y * (v.w - mu) * rs;
+      ab.x += a.x; ab.y += a.y; ab.z += c.x; ab.w += c.y;
+    }
+    if (++t == sg.seq) { t = 0; ++bidx; }
+  }
+  atomicAdd(dw + col, aw.x); atomicAdd(dw + col + 1, aw.y); atomicAdd(dw + col + 2, aw.z); atomicAdd(dw + col + 3, aw.w);
+  atomicAdd(db + col, ab.x); atomicAdd(db + col + 1, ab.y); atomicAdd(db + col + 2, ab.z); atomicAdd(db + col + 3, ab.w);
 }
 
 // d_o = bf16(dy * scale); dscale += colsum(dy * o); dbias += colsum(dy * scale).   thread = 4 columns
@@ -413,11 +419,17 @@ extern "C" int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2
   if (D % 128 || D > 128 * MAXV) return -41;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
-  int blocks = 148 * 4;
-  const int rows_per_block = 8;
-  if (blocks > (M + rows_per_block - 1) / rows_per_block) blocks = (M + rows_per_block - 1) / rows_per_block;
-  ln_shift_bwd_kernel<<<blocks, 256, 2 * D * sizeof(float), st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2,
-                                                                   mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode);
+  const int threads = 256, rows_per_block = threads / 32;
+  const int blocks = (M + rows_per_block - 1) / rows_per_block;
+  ln_shift_bwd_dx_kernel<<<blocks, threads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2, mean, rstd, w,
+                                                     dx, dx2, M, D, sg, mode);
+  int cthreads = 256;
+  if (D < cthreads * 4) cthreads = D / 4;
+  const int stripes = D / (cthreads * 4);
+  int nsplit = (148 * 8) / stripes;
+  if (nsplit > M) nsplit = M;
+  ln_shift_bwd_dwdb_kernel<<<stripes * nsplit, cthreads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2,
+                                                                  mean, rstd, dw, db, M, D, sg);
   return err();
 }
 

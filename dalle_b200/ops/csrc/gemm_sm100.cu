@@ -9,7 +9,8 @@
 // Persistent kernel: grid = min(#work units, #SMs); each CTA has 6 warps:
 //   warp 0  : TMA producer            (one lane)
 //   warp 1  : TMEM allocator + MMA issuer (one lane)
-//   warps 2-5: epilogue, warp w owns TMEM lanes 32*(w%4)..+31 (one output row per thread)
+//   warps 2-9: epilogue, warp w owns TMEM lanes 32*(w%4)..+31 (one output row per thread) and one half of the
+//              256 accumulator columns
 #include "sm100_ptx.cuh"
 #include "b200_api.h"
 
@@ -24,7 +25,7 @@ constexpr int STAGES = 4;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 
@@ -38,8 +39,9 @@ struct GemmDev {
   const float* bias;
   const float* scale;
   const float* res;  long long ldres;
-  const float2* rot;  // [seq_len][32] (cos, sin) per pair
+  const float2* rot;  // TRANSPOSED table [32 pairs][rot_len] of (cos, sin): lanes = consecutive rows -> coalesced
   int seq_len;
+  int rot_len;
   int q_cols;          // columns < q_cols are scaled by q_scale (rotary epilogue)
   float q_scale;
   const __nv_bfloat16* aux;  long long ldaux;
@@ -115,7 +117,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 128);
+      mbar_init(&tempty_bar[s], 256);
     }
     fence_barrier_init();
   }
@@ -206,6 +208,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   } else {
     // ------------------------------- epilogue warps -------------------------------------------
     const int q = warp & 3;
+    const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -221,7 +224,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (EPI == B200_EPI_GEGLU) {
         // accumulator columns [0,128) = value half, [128,256) = gate half (same 128 output columns)
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = chalf * 2; c < chalf * 2 + 2; ++c) {
           uint32_t ra[32], rg[32];
           tmem_ld32(taddr + c * 32, ra);
           tmem_ld32(taddr + 128 + c * 32, rg);
@@ -245,7 +248,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       } else {
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
+        for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
           const int col = n0 + c * 32;
           if (col >= g.N) break;  // warp-uniform
           uint32_t r[32];
@@ -271,12 +274,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             // interleaved-pair rotary on q, k and v; q additionally scaled (dalle-pytorch applies
             // rotary to v as well)
             const int pos = row % g.seq_len;
-            const float2* rt = g.rot + (long long)pos * 32 + ((col & 63) >> 1);
+            const float2* rt = g.rot + (long long)((col & 63) >> 1) * g.rot_len + pos;
             const float s = (col < g.q_cols) ? g.q_scale : 1.0f;
             float o[32];
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
-              const float2 cs = __ldg(rt + (j >> 1));
+              const float2 cs = __ldg(rt + (long long)(j >> 1) * g.rot_len);
               const float x0 = v[j] + (g.bias ? __ldg(g.bias + col + j) : 0.f);
               const float x1 = v[j + 1] + (g.bias ? __ldg(g.bias + col + j + 1) : 0.f);
               o[j] = (x0 * cs.x - x1 * cs.y) * s;
@@ -517,6 +520,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   g.bias = d->bias; g.scale = d->scale;
   g.res = d->res; g.ldres = d->ldres;
   g.rot = reinterpret_cast<const float2*>(d->rot); g.seq_len = d->seq_len > 0 ? d->seq_len : 1;
+  g.rot_len = d->rot_len;
   g.q_cols = d->q_cols; g.q_scale = d->q_scale;
   g.aux = reinterpret_cast<const __nv_bfloat16*>(d->aux); g.ldaux = d->ldaux;
   g.n_half = d->n_half;

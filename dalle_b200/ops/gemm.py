@@ -18,6 +18,19 @@ NT, NN, TN = 0, 1, 2
 EPI_BF16, EPI_F32, EPI_ATOMIC_F32, EPI_ROTARY, EPI_RESID, EPI_GEGLU, EPI_GEGLU_BWD = range(7)
 
 
+_ROT_T = {}
+
+
+def rot_transposed(rot: torch.Tensor) -> torch.Tensor:
+    """[n, 32, 2] -> pair-major [32, n, 2] copy (cached): consecutive rows become contiguous for the epilogue."""
+    key = (rot.data_ptr(), tuple(rot.shape), str(rot.device))
+    t = _ROT_T.get(key)
+    if t is None:
+        t = rot.permute(1, 0, 2).contiguous()
+        _ROT_T[key] = t
+    return t
+
+
 def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else t.data_ptr()
 
@@ -124,7 +137,10 @@ def gemm(mode: int, epi: int, A: torch.Tensor, B: torch.Tensor, out: torch.Tenso
     d.out2, d.ldo2 = _ptr(out2), _ld(out2)
     d.bias, d.scale = _ptr(bias), _ptr(scale)
     d.res, d.ldres = _ptr(res), _ld(res)
-    d.rot, d.seq_len, d.q_cols, d.q_scale = _ptr(rot), seq_len, q_cols, q_scale
+    if rot is not None:
+        rot_t = rot_transposed(rot)
+        d.rot, d.rot_len = rot_t.data_ptr(), rot_t.shape[1]
+    d.seq_len, d.q_cols, d.q_scale = seq_len, q_cols, q_scale
     d.aux, d.ldaux = _ptr(aux), _ld(aux)
     d.n_half, d.alpha, d.splits = n_half, alpha, splits
     rc = lib.cuda_lib().b200_gemm_bf16(ctypes.byref(d), torch.cuda.current_stream().cuda_stream)

@@ -43,8 +43,8 @@ typedef struct B200Gemm {
   const float* bias;   /* [N] (GEGLU: [2*n_half]) or NULL */
   const float* scale;  /* [N] LayerScale (RESID)           */
   const float* res; long long ldres; /* fp32 residual (RESID) */
-  const void* rot;     /* float2[seq_len][32] = (cos, sin) per interleaved pair (ROTARY) */
-  int seq_len; int q_cols; float q_scale;
+  const void* rot;     /* float2[32][rot_len] = (cos, sin) per interleaved pair, pair-major (ROTARY) */
+  int seq_len; int rot_len; int q_cols; float q_scale;
   const void* aux; long long ldaux; /* bf16 [M, 2*n_half] (GEGLU_BWD) */
   int n_half;          /* GEGLU: N counts value columns only; B has 2*n_half rows */
   float alpha;
@@ -67,7 +67,7 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq,
  * Scratch: delta fp32 [B,H,seq]; kv_acc fp32 [B*seq, 2*H*64] which must be all-zero on entry and is returned
  * all-zero (gradients of keys shared between CTAs are reduced there with red.add before conversion). */
 int b200_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
-                  float* kv_acc, const void* rot, float q_scale, int B, int H, int seq, int T, int F, int mode,
+                  float* kv_acc, const void* rot /* [seq+1][32] */, const void* rot_t /* [32][seq+1] */, float q_scale, int B, int H, int seq, int T, int F, int mode,
                   int conv_kernel, void* stream);
 
 /* ------------------------------------------------------------------------------------------------

@@ -1,0 +1,72 @@
+"""GPU micro-benchmarks of individual ops at TTT shapes (CUDA events, warm)."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from dalle_b200.config import ttt_config
+from dalle_b200.ops import attention as A, elementwise as E, gemm as G
+from dalle_b200.models.rotary import rotary_pair_table
+
+
+def timeit(fn, iters=10):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(True), torch.cuda.Event(True)
+    s.record()
+    for _ in range(iters): fn()
+    e.record(); torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters * 1e3  # us
+
+
+def main():
+    B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+    cfg = ttt_config()
+    M, D, I = B * cfg.seq_len, cfg.dim, cfg.inner_dim
+    dev = "cuda"
+    qkv = torch.zeros(M + 128, 3 * I, device=dev, dtype=torch.bfloat16)
+    qkv[:M] = (torch.randn(M, 3 * I, device=dev) * 0.5).bfloat16()
+    out = torch.zeros(M, I, device=dev, dtype=torch.bfloat16)
+    lse = torch.zeros(B, cfg.heads, cfg.seq_len, device=dev)
+    dout = torch.zeros(M + 128, I, device=dev, dtype=torch.bfloat16)
+    dout[:M] = torch.randn(M, I, device=dev).bfloat16()
+    delta = torch.zeros_like(lse)
+    dqkv = torch.zeros(M, 3 * I, device=dev, dtype=torch.bfloat16)
+    kv_acc = torch.zeros(M, 2 * I, device=dev)
+    rot = rotary_pair_table(cfg).cuda()
+    for t in ("axial_row", "axial_col", "conv_like"):
+        f = timeit(lambda: A.attn_fwd(qkv, out, lse, cfg, t))
+        b = timeit(lambda: A.attn_bwd(qkv, out, dout, lse, delta, dqkv, kv_acc, rot, cfg, t))
+        print(f"attn {t}: fwd {f:.0f} us  bwd {b:.0f} us", flush=True)
+    x = torch.randn(M, D, device=dev); w = torch.ones(D, device=dev); bb = torch.zeros(D, device=dev)
+    h = torch.zeros(M, D, device=dev, dtype=torch.bfloat16); mean = torch.zeros(M, device=dev); rstd = torch.zeros(M, device=dev)
+    print(f"ln_shift_fwd {timeit(lambda: E.ln_shift_fwd(x, None, w, bb, h, mean, rstd, cfg, True)):.0f} us")
+    dx = torch.zeros(M, D, device=dev); dw = torch.zeros(D, device=dev); db = torch.zeros(D, device=dev)
+    print(f"ln_shift_bwd {timeit(lambda: E.ln_shift_bwd(h, x, None, mean, rstd, w, dx, None, dw, db, cfg, True, 0)):.0f} us")
+    # GEMM epilogue variants
+    W1 = (torch.randn(8192, D, device=dev) * 0.03).bfloat16(); b1 = torch.zeros(8192, device=dev)
+    u = torch.zeros(M, 4096, device=dev, dtype=torch.bfloat16); pre = torch.zeros(M, 8192, device=dev, dtype=torch.bfloat16)
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_GEGLU, h, W1, u, out2=pre, bias=b1, n_half=4096))
+    print(f"FF1 GEGLU (+pre) {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_GEGLU, h, W1, u, bias=b1, n_half=4096))
+    print(f"FF1 GEGLU        {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
+    W2 = (torch.randn(D, 4096, device=dev) * 0.03).bfloat16(); sc = torch.ones(D, device=dev)
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_RESID, u, W2, x, bias=bb, scale=sc, res=x, alpha=1.0))
+    print(f"FF2 RESID        {t_:.0f} us  {2*M*4096*D/t_/1e6:.0f} TF/s")
+    Wq = (torch.randn(3 * I, D, device=dev) * 0.03).bfloat16()
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_ROTARY, h, Wq, qkv[:M], rot=rot, seq_len=cfg.seq_len, q_cols=I, q_scale=0.125))
+    print(f"QKV ROTARY       {t_:.0f} us  {2*M*3*I*D/t_/1e6:.0f} TF/s")
+    d_o = torch.randn(M, D, device=dev).bfloat16(); dpre = torch.zeros(M, 8192, device=dev, dtype=torch.bfloat16)
+    t_ = timeit(lambda: G.gemm(G.NN, G.EPI_GEGLU_BWD, d_o, W2, dpre, aux=pre, n_half=4096))
+    print(f"GEGLU_BWD dgrad  {t_:.0f} us  {2*M*4096*D/t_/1e6:.0f} TF/s")
+    dh = torch.zeros(M, D, device=dev, dtype=torch.bfloat16)
+    t_ = timeit(lambda: G.gemm(G.NN, G.EPI_BF16, dpre, W1, dh))
+    print(f"dgrad FF1        {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
+    gW1 = torch.zeros(8192, D, device=dev)
+    t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, dpre, h, gW1))
+    print(f"wgrad FF1        {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
+    gWo = torch.zeros(D, D, device=dev)
+    t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, d_o, h, gWo))
+    print(f"wgrad 1024x1024  {t_:.0f} us  {2*M*D*D/t_/1e6:.0f} TF/s")
+
+
+if __name__ == "__main__":
+    main()
