@@ -97,7 +97,13 @@ class DHT:
                 fut.result(2.0)
             except Exception:
                 pass
-            self._loop.call_soon_threadsafe(self._loop.stop)
+
+            def _cancel_all():
+                for t in asyncio.all_tasks(self._loop):
+                    t.cancel()
+                self._loop.call_later(0.05, self._loop.stop)
+
+            self._loop.call_soon_threadsafe(_cancel_all)
         if self._thread is not None:
             self._thread.join(2.0)
         self.is_alive = False
