@@ -1,0 +1,87 @@
+"""T2: collaborative optimizer end to end on localhost - epochs advance in lock-step, weighted gradient averaging is
+correct, a late joiner downloads state, state_dict layout carries local_epoch."""
+import threading
+import time
+
+import torch
+
+from dalle_b200.collab import Float16Compression, Optimizer, SizeAdaptiveCompression, Uniform8BitQuantization
+from dalle_b200.dht import DHT
+
+
+def _dht(peers=()):
+    return DHT(initial_peers=list(peers), start=True, host_maddrs=["/ip4/127.0.0.1/tcp/0"])
+
+
+def _make(dht, run_id, bs, target=32, lr=0.1, **kw):
+    torch.manual_seed(0)
+    model = torch.nn.Linear(8, 1)
+    opt = Optimizer(dht=dht, run_id=run_id, target_batch_size=target, batch_size_per_step=bs,
+                    optimizer=lambda params: torch.optim.SGD(params, lr=lr), params=list(model.parameters()),
+                    scheduler=lambda o: torch.optim.lr_scheduler.LambdaLR(o, lambda e: 1.0),
+                    matchmaking_time=1.5, averaging_timeout=15, allreduce_timeout=10, reuse_grad_buffers=True,
+                    delay_optimizer_step=True, target_group_size=kw.pop("group", None),
+                    tracker_opts=dict(min_refresh_period=0.1, default_refresh_period=0.3, max_refresh_period=0.5), **kw)
+    return model, opt
+
+
+def test_two_peers_advance_in_lockstep_with_weighted_average():
+    d0 = _dht()
+    d1 = _dht([str(m) for m in d0.get_visible_maddrs()])
+    try:
+        (m0, o0), (m1, o1) = _make(d0, "lock", bs=8, group=2), _make(d1, "lock", bs=8, group=2)
+        w_init = m0.weight.detach().clone()
+        stop, errors = threading.Event(), []
+
+        def train(model, opt, gval):
+            try:
+                while not stop.is_set() and opt.local_epoch < 2:
+                    for p in model.parameters():
+                        p.grad = torch.full_like(p, gval) if p.grad is None else p.grad.add_(gval)
+                    opt.step()
+                    time.sleep(0.05)
+            except Exception as e:  # pragma: no cover
+                errors.append(e)
+
+        ts = [threading.Thread(target=train, args=(m0, o0, 1.0)), threading.Thread(target=train, args=(m1, o1, 3.0))]
+        [t.start() for t in ts]
+        [t.join(60) for t in ts]
+        stop.set()
+        assert not errors, errors
+        assert o0.local_epoch >= 2 and o1.local_epoch >= 2
+        # each epoch: averaged gradient = sample-weighted mean of per-peer mean grads, between 1 and 3
+        delta = (w_init - m0.weight.detach()) / 0.1 / o0.local_epoch
+        assert 0.99 <= delta.mean().item() <= 3.01
+        o0._finish_pending(); o1._finish_pending()
+        assert torch.allclose(m0.weight, m1.weight, atol=1e-4), (m0.weight, m1.weight)
+        sd = o0.state_dict()
+        assert sd["state"]["local_epoch"] == o0.local_epoch
+        o0.shutdown(); o1.shutdown()
+    finally:
+        d0.shutdown(); d1.shutdown()
+
+
+def test_single_peer_uses_local_gradients_and_late_joiner_loads_state():
+    d0 = _dht()
+    try:
+        m0, o0 = _make(d0, "solo", bs=16, target=32, averager_opts=dict(declare_state_period=0.5))
+        for _ in range(6):
+            for p in m0.parameters():
+                p.grad = torch.ones_like(p) if p.grad is None else p.grad.add_(1.0)
+            o0.step()
+        assert o0.local_epoch == 3
+        assert o0.grad_averager.local_samples_accumulated == 0
+        o0.state_averager.declare_state_now()
+        d1 = _dht([str(m) for m in d0.get_visible_maddrs()])
+        m1, o1 = _make(d1, "solo", bs=16, target=32)
+        time.sleep(0.5)
+        assert o1.load_state_from_peers()
+        assert o1.local_epoch == 3 and torch.allclose(m1.weight, m0.weight)
+        o0.shutdown(); o1.shutdown(); d1.shutdown()
+    finally:
+        d0.shutdown()
+
+
+def test_compression_choice_matches_reference_threshold():
+    c = SizeAdaptiveCompression(threshold=2 ** 16 + 1, less=Float16Compression(), greater_equal=Uniform8BitQuantization())
+    assert c.choose(65536).name == "fp16" and c.choose(65537).name == "u8"
