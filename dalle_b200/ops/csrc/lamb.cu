@@ -8,64 +8,14 @@
 //   trust  : r = clamp(||p||, 0, clamp) / ||u||  (1 if either is 0) ; p <- p - lr * r * u   (lamb_8bit.py:149-158)
 // Layout: every tensor starts on a 4096-element boundary of the flat buffer, so a CUDA block == a quantisation
 // block == part of exactly one tensor.  Three launches: grad-norm (+finite flag) / moments+u / apply.
-#include "sm100_ptx.cuh"
 #include "b200_api.h"
 
 #include <cstdio>
 #include <mutex>
 
+#include "lamb_device.cuh"
+
 namespace b200 {
-
-constexpr int QBLOCK = 4096;
-constexpr int LAMB_THREADS = 256;
-constexpr int EPT = QBLOCK / LAMB_THREADS;  // 16 elements per thread
-
-__device__ __forceinline__ float block_sum(float v, float* sred) {
-  v = warp_sum(v);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) sred[warp] = v;
-  __syncthreads();
-  float t = 0.f;
-  if (warp == 0) {
-    t = lane < (blockDim.x >> 5) ? sred[lane] : 0.f;
-    t = warp_sum(t);
-    if (lane == 0) sred[0] = t;
-  }
-  __syncthreads();
-  return sred[0];
-}
-__device__ __forceinline__ float block_max(float v, float* sred) {
-  v = warp_max(v);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) sred[warp] = v;
-  __syncthreads();
-  float t = 0.f;
-  if (warp == 0) {
-    t = lane < (blockDim.x >> 5) ? sred[lane] : -1e38f;
-    t = warp_max(t);
-    if (lane == 0) sred[0] = t;
-  }
-  __syncthreads();
-  return sred[0];
-}
-
-// nearest entry of a sorted 256-entry code (bitsandbytes quantize_cpu: lower bound, then compare neighbours)
-__device__ __forceinline__ int nearest_code(const float* code, float x) {
-  int lo = 0, hi = 255;  // find largest idx with code[idx] <= x (clamped)
-#pragma unroll
-  for (int it = 0; it < 8; ++it) {
-    const int mid = (lo + hi + 1) >> 1;
-    if (code[mid] <= x) lo = mid; else hi = mid - 1;
-  }
-  int idx = lo;
-  if (idx < 255) {
-    const float dl = fabsf(x - code[idx]), dr = fabsf(x - code[idx + 1]);
-    if (dr < dl) idx += 1;
-  }
-  return idx;
-}
 
 // stats[0] += sum g^2 ; stats[1] = 1 if any non-finite value was seen
 __global__ void __launch_bounds__(LAMB_THREADS)
@@ -83,19 +33,6 @@ lamb_grad_norm_kernel(const float* __restrict__ g, long long n, float* __restric
   if (threadIdx.x == 0) atomicAdd(&stats[0], s);
   if (bad) stats[1] = 1.f;
 }
-
-struct LambBlock {   // one entry per 4096-element block of the flat buffer
-  int tensor;        // tensor index
-  int valid;         // valid elements in this block
-  long long state_off;  // offset into the uint8 state (quantised) or fp32 state (small tensors)
-  int quantized;
-  int absmax_idx;
-};
-
-struct LambHyper {
-  float beta1, beta2, eps, max_grad_norm, clamp_value, lr, grad_scale;
-  int use_clip;
-};
 
 __global__ void __launch_bounds__(LAMB_THREADS)
 lamb_moments_kernel(float* __restrict__ g, const float* __restrict__ p, uint8_t* __restrict__ q1,

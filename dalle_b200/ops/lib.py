@@ -33,6 +33,24 @@ class B200Gemm(ctypes.Structure):
     ]
 
 
+class B200Group(ctypes.Structure):
+    _fields_ = [
+        ("rank", ctypes.c_int), ("world", ctypes.c_int),
+        ("grad_ptrs", ctypes.c_void_p * 8), ("param_ptrs", ctypes.c_void_p * 8), ("shadow_ptrs", ctypes.c_void_p * 8),
+        ("payload_ptrs", ctypes.c_void_p * 8), ("signal_ptrs", ctypes.c_void_p * 8), ("xchg_ptrs", ctypes.c_void_p * 8),
+        ("xstride", ctypes.c_int), ("n_tensors", ctypes.c_int), ("n_blocks", ctypes.c_int),
+        ("blk0", ctypes.c_int), ("blk1", ctypes.c_int), ("epoch", ctypes.c_uint), ("payload_mode", ctypes.c_int),
+        ("zero_grad", ctypes.c_int),
+        ("q1", ctypes.c_void_p), ("q2", ctypes.c_void_p), ("f1", ctypes.c_void_p), ("f2", ctypes.c_void_p),
+        ("absmax1", ctypes.c_void_p), ("absmax2", ctypes.c_void_p), ("code1", ctypes.c_void_p),
+        ("code2", ctypes.c_void_p), ("blocks", ctypes.c_void_p), ("wd_per_tensor", ctypes.c_void_p),
+        ("tensor_sums", ctypes.c_void_p), ("stats", ctypes.c_void_p), ("trust_out", ctypes.c_void_p),
+        ("beta1", ctypes.c_float), ("beta2", ctypes.c_float), ("eps", ctypes.c_float),
+        ("max_grad_norm", ctypes.c_float), ("clamp_value", ctypes.c_float), ("lr", ctypes.c_float),
+        ("grad_scale", ctypes.c_float),
+    ]
+
+
 def _try_build():
     if os.environ.get("DALLE_B200_NO_AUTOBUILD"):
         return
@@ -94,6 +112,7 @@ _f = ctypes.c_float
 
 class _Sigs:
     b200_gemm_bf16 = [ctypes.POINTER(B200Gemm), _p]
+    b200_group_lamb_step = [ctypes.POINTER(B200Group), _p]
     b200_attn_fwd = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
     b200_ln_shift_fwd = [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _f, _p]
     b200_ln_shift_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p]

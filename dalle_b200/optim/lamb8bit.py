@@ -144,6 +144,24 @@ class FlatLayout:
                     p._bf16_shadow.copy_(p.detach())
                     p._shadow_version = p._version
 
+    @torch.no_grad()
+    def rebind(self, flat: torch.Tensor, flat_grad: torch.Tensor, flat_bf16: Optional[torch.Tensor]):
+        """Move the storage to caller-provided buffers (e.g. NVLink symmetric memory); views are re-pointed."""
+        assert flat.numel() >= self.n_padded and flat_grad.numel() >= self.n_padded
+        flat[: self.n_padded].copy_(self.flat)
+        flat_grad[: self.n_padded].copy_(self.flat_grad)
+        if flat_bf16 is not None and self.flat_bf16 is not None:
+            flat_bf16[: self.n_padded].copy_(self.flat_bf16)
+        self.flat, self.flat_grad = flat[: self.n_padded], flat_grad[: self.n_padded]
+        self.flat_bf16 = flat_bf16[: self.n_padded] if flat_bf16 is not None else None
+        for p, o in zip(self.params, self.offsets):
+            n = p.numel()
+            p.data = self.flat[o:o + n].view(p.shape)
+            p.grad = self.flat_grad[o:o + n].view(p.shape)
+            if self.flat_bf16 is not None:
+                p._bf16_shadow = self.flat_bf16[o:o + n].view(p.shape)
+                p._shadow_version = p._version
+
     def mark_shadows_fresh(self):
         for p in self.params:
             if self.flat_bf16 is not None:

@@ -116,6 +116,30 @@ int b200_lamb_step(float* grad, float* param, void* param_bf16, long long n_padd
                    float* trust_out, float* stats, float beta1, float beta2, float eps, float max_grad_norm,
                    float clamp_value, float lr, float grad_scale, int zero_grad, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Fused intra-box step (group_avg.cu): gradient reduce-scatter over NVLink peer memory -> LAMB-8bit on this rank's
+ * shard -> parameter all-gather with P2P stores, as ONE cooperative kernel per rank; no NCCL call on the path.
+ * Replaces nn.DataParallel's reduce/broadcast inside a box (reference lib/training/hf_trainer.py:35-38 via HF
+ * Trainer) and the CPU optimizer step after averaging (reference lib/training/lamb_8bit.py:83-158).
+ * All *_ptrs[r] are rank r's copies of symmetric (peer-mapped) allocations; signal_ptrs[r] holds >= world uint32
+ * slots that start at zero; xchg_ptrs[r] holds world * xstride floats; epoch must grow by 4 with every call.
+ * Every rank of the box must launch the kernel for the same step (the ranks wait for each other in device code).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct B200Group {
+  int rank, world;
+  void* grad_ptrs[8]; void* param_ptrs[8]; void* shadow_ptrs[8]; void* payload_ptrs[8];
+  void* signal_ptrs[8]; void* xchg_ptrs[8];
+  int xstride, n_tensors, n_blocks, blk0, blk1;
+  unsigned int epoch;
+  int payload_mode;   /* 0: fp32 gradients read over NVLink; 1: bf16 payload (half the bytes) */
+  int zero_grad;
+  void* q1; void* q2; float* f1; float* f2; float* absmax1; float* absmax2;
+  const float* code1; const float* code2; const void* blocks; const float* wd_per_tensor;
+  float* tensor_sums; float* stats /* [4] */; float* trust_out;
+  float beta1, beta2, eps, max_grad_norm, clamp_value, lr, grad_scale;
+} B200Group;
+int b200_group_lamb_step(const B200Group* desc, void* stream);
+
 /* b200_lamb_step for callers that cannot provide scratch memory.  No counterpart in the reference: it exists for
  * embedders of this library that may not allocate device memory once they are running (all of it belongs to their
  * own pool, or an allocation inside the optimizer step could fail or stall the device).  The two work arrays of

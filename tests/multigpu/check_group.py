@@ -1,0 +1,73 @@
+"""Run under torchrun (N ranks, one GPU each): fused NVLink averaging + sharded LAMB vs NCCL all-reduce + the
+single-GPU LAMB kernels (T4).  Prints GROUP_OK on rank 0 when everything matches."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch
+import torch.distributed as dist
+
+from dalle_b200.optim.lamb8bit import LAMB8Bit
+from dalle_b200.parallel.group import FusedGroupAverager
+from dalle_b200.trainer import init_distributed_from_env
+
+
+def make(dev, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    shapes = [(300, 256), (70001,), (1024,), (1, 1, 256), (4096 * 21 + 3,), (513, 1024)]
+    ps = [torch.nn.Parameter((torch.randn(*s, generator=g) * 0.1).to(dev)) for s in shapes]
+    opt = LAMB8Bit([{"params": ps[:4], "weight_decay": 0.045}, {"params": ps[4:], "weight_decay": 0.0}], lr=1e-2,
+                   betas=(0.9, 0.96), eps=1e-6, weight_decay=0.045, max_grad_norm=0.5, clamp_value=10000.0)
+    opt._build_fused()
+    return ps, opt
+
+
+def main():
+    payload = sys.argv[1] if len(sys.argv) > 1 else "fp32"
+    rank, local, world = init_distributed_from_env()
+    dev = torch.device("cuda", local)
+    ps_a, opt_a = make(dev)
+    ps_b, opt_b = make(dev)
+    group = FusedGroupAverager(opt_a, payload=payload)
+    for step in range(3):
+        g = torch.Generator().manual_seed(1000 * step + rank)
+        grads = [(torch.randn(p.shape, generator=g) * 0.05).to(dev) for p in ps_a]
+        for p, q, gr in zip(ps_a, ps_b, grads):
+            p.grad.copy_(gr)
+            q.grad.copy_(gr)
+        group.step(grad_scale=1.0 / world)
+        flat_b = opt_b._fused.layout.flat_grad
+        dist.all_reduce(flat_b)
+        opt_b.step(grad_scale=1.0 / world, zero_grad=True)
+        torch.cuda.synchronize()
+        assert not group.step_was_skipped()
+        La, Lb = opt_a._fused.layout, opt_b._fused.layout
+        tol = 1e-3 if payload == "fp32" else 3e-3
+        err = (La.flat - Lb.flat).abs().max().item()
+        assert err < tol, f"step {step}: fused vs nccl path differ by {err}"
+        assert La.flat_grad.abs().max().item() == 0.0
+        assert torch.equal(La.flat_bf16.float(), La.flat.to(torch.bfloat16).float())
+        # every rank must hold bit-identical parameters after the all-gather
+        mine = La.flat.clone()
+        ref = mine.clone()
+        dist.broadcast(ref, src=0)
+        assert torch.equal(mine, ref), "ranks diverged"
+        gn_a, gn_b = group.grad_norm(), opt_b.grad_norm()
+        assert abs(gn_a - gn_b) / gn_b < (1e-4 if payload == "fp32" else 1e-2), (gn_a, gn_b)
+    # non-finite gradient on ONE rank: every rank skips the step
+    before = opt_a._fused.layout.flat.clone()
+    for p in ps_a:
+        p.grad.normal_()
+    if rank == world - 1:
+        ps_a[0].grad[0, 0] = float("inf")
+    group.step(grad_scale=1.0 / world)
+    torch.cuda.synchronize()
+    assert group.step_was_skipped() and torch.equal(before, opt_a._fused.layout.flat)
+    dist.barrier()
+    if rank == 0:
+        print(f"GROUP_OK world={world} payload={payload}")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
