@@ -52,7 +52,7 @@ def main():
         ref = mine.clone()
         dist.broadcast(ref, src=0)
         assert torch.equal(mine, ref), "ranks diverged"
-        gn_a, gn_b = group.grad_norm(), opt_b.grad_norm()
+        gn_a, gn_b = group.grad_norm(), opt_b.grad_norm() / world  # the single-GPU entry reports the unscaled norm
         assert abs(gn_a - gn_b) / gn_b < (1e-4 if payload == "fp32" else 1e-2), (gn_a, gn_b)
     # non-finite gradient on ONE rank: every rank skips the step
     before = opt_a._fused.layout.flat.clone()
