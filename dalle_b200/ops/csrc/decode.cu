@@ -1,0 +1,306 @@
+// Single-token decode kernels for KV-cached sampling (replaces the ~2000 eager launches
+// per token of dalle-pytorch's cached forward + top-k/gumbel sampling used by reference inference/run_inference.py).
+// Every kernel reads the current position from DEVICE memory so that one whole decode step (64 layers + head +
+// sampler) is captured once in a CUDA graph and replayed 1281 times.
+//
+//   decode_embed      x1 = x2 = W[ids[b, pos]]
+//   decode_ln_shift   LN of one token per sample + token shift from the per-block cache of earlier normalised tokens
+//   decode_attn       append (k, v) of the token to the layer's cache, then attention over the keys the sparsity
+//                     pattern allows at this position (all text keys + row prefix / column prefix / conv window)
+//   decode_sample     temperature / top-k / top-p / multinomial over the image-vocabulary logits
+//   decode_advance    pos += 1
+#include "sm100_ptx.cuh"
+#include "b200_api.h"
+
+namespace b200 {
+
+constexpr float kLog2eDec = 1.4426950408889634f;
+
+struct DecGeom {
+  int B, D, H, seq, T, F, conv_half;
+};
+
+__global__ void decode_embed_kernel(const long long* __restrict__ ids, int ids_stride, const float* __restrict__ W,
+                                    float* __restrict__ x1, float* __restrict__ x2, const int* __restrict__ pos_ptr,
+                                    int B, int D) {
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (b >= B) return;
+  const long long id = ids[static_cast<long long>(b) * ids_stride + *pos_ptr];
+  for (int c = lane * 4; c < D; c += 128) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(W + id * D + c));
+    *reinterpret_cast<float4*>(x1 + static_cast<long long>(b) * D + c) = v;
+    *reinterpret_cast<float4*>(x2 + static_cast<long long>(b) * D + c) = v;
+  }
+}
+
+// cache: [B, seq, D/2] bf16 holding the first half of the channels of every earlier normalised token
+__global__ void decode_ln_shift_kernel(const float* __restrict__ x, const float* __restrict__ x2,
+                                       const float* __restrict__ w, const float* __restrict__ bias,
+                                       __nv_bfloat16* __restrict__ cache, __nv_bfloat16* __restrict__ out,
+                                       const int* __restrict__ pos_ptr, DecGeom g, float eps, int shift) {
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (b >= g.B) return;
+  const int pos = *pos_ptr, D = g.D;
+  const int nv = D / 128;
+  float4 v[8];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (k < nv) {
+      const long long off = static_cast<long long>(b) * D + k * 128 + lane * 4;
+      v[k] = *reinterpret_cast<const float4*>(x + off);
+      if (x2) {
+        const float4 u = *reinterpret_cast<const float4*>(x2 + off);
+        v[k] = make_float4(0.5f * (v[k].x + u.x), 0.5f * (v[k].y + u.y), 0.5f * (v[k].z + u.z), 0.5f * (v[k].w + u.w));
+      }
+      s += v[k].x + v[k].y + v[k].z + v[k].w;
+    }
+  }
+  const float mu = warp_sum(s) / D;
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (k < nv) {
+      const float a = v[k].x - mu, c = v[k].y - mu, d = v[k].z - mu, e = v[k].w - mu;
+      q += a * a + c * c + d * d + e * e;
+    }
+  const float rs = rsqrtf(warp_sum(q) / D + eps);
+  // which earlier positions feed the shifted channels
+  int src_a = -1, src_b = -1;  // source position for channels [0, D/4) and [D/4, D/2)
+  if (shift) {
+    if (pos < g.T) {
+      src_a = src_b = pos >= 1 ? pos - 1 : -1;
+    } else {
+      const int p = pos - g.T, r = p / g.F, c = p - r * g.F;
+      src_a = r >= 1 ? pos - g.F : -1;
+      src_b = c >= 1 ? pos - 1 : -1;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (k < nv) {
+      const int col = k * 128 + lane * 4;
+      const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
+      const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + col));
+      uint2 o;
+      o.x = pack_bf16x2((v[k].x - mu) * rs * ww.x + bb.x, (v[k].y - mu) * rs * ww.y + bb.y);
+      o.y = pack_bf16x2((v[k].z - mu) * rs * ww.z + bb.z, (v[k].w - mu) * rs * ww.w + bb.w);
+      if (shift && col < D / 2) {
+        __nv_bfloat16* crow = cache + (static_cast<long long>(b) * g.seq + pos) * (D / 2) + col;
+        *reinterpret_cast<uint2*>(crow) = o;  // remember this token's own normalised half for later positions
+        const int src = col < D / 4 ? src_a : src_b;
+        if (src >= 0)
+          o = *reinterpret_cast<const uint2*>(cache + (static_cast<long long>(b) * g.seq + src) * (D / 2) + col);
+        else
+          o = make_uint2(0u, 0u);
+      }
+      *reinterpret_cast<uint2*>(out + static_cast<long long>(b) * D + col) = o;
+    }
+  }
+}
+
+// one warp per (sample, head); each lane owns 2 of the 64 head dims for the output, keys are processed one by one
+// by the whole warp (dot product = 2 FMAs per lane + warp reduce).  n_keys <= 257 + 32 (+ conv window).
+__global__ void decode_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ kcache,
+                                   __nv_bfloat16* __restrict__ vcache, __nv_bfloat16* __restrict__ out,
+                                   const int* __restrict__ pos_ptr, DecGeom g, int mode) {
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (wid >= g.B * g.H) return;
+  const int b = wid / g.H, h = wid - b * g.H, pos = *pos_ptr;
+  const int HD = g.H * 64;
+  const __nv_bfloat16* row = qkv + static_cast<long long>(b) * 3 * HD + h * 64 + lane * 2;
+  const float2 q = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(row));
+  const uint32_t kk = *reinterpret_cast<const uint32_t*>(row + HD);
+  const uint32_t vv = *reinterpret_cast<const uint32_t*>(row + 2 * HD);
+  const long long cbase = (static_cast<long long>(b) * g.H + h) * g.seq * 64;
+  *reinterpret_cast<uint32_t*>(kcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) = kk;
+  *reinterpret_cast<uint32_t*>(vcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) = vv;
+  __syncwarp();
+
+  float m = -1e30f, l = 0.f, a0 = 0.f, a1 = 0.f;
+  auto visit = [&](int j) {
+    const uint32_t ku = (j == pos) ? kk : *reinterpret_cast<const uint32_t*>(kcache + cbase + static_cast<long long>(j) * 64 + lane * 2);
+    const uint32_t vu = (j == pos) ? vv : *reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(j) * 64 + lane * 2);
+    const float2 kf = unpack_bf16x2(ku), vf = unpack_bf16x2(vu);
+    const float s = warp_sum(q.x * kf.x + q.y * kf.y) * kLog2eDec;
+    const float mn = fmaxf(m, s);
+    const float corr = exp2f(m - mn), p = exp2f(s - mn);
+    l = l * corr + p;
+    a0 = a0 * corr + p * vf.x;
+    a1 = a1 * corr + p * vf.y;
+    m = mn;
+  };
+  if (pos < g.T) {
+    for (int j = 0; j <= pos; ++j) visit(j);
+  } else {
+    for (int j = 0; j < g.T; ++j) visit(j);
+    const int p = pos - g.T, r = p / g.F, c = p - r * g.F;
+    if (mode == 1) {
+      for (int cc = 0; cc <= c; ++cc) visit(g.T + r * g.F + cc);
+    } else if (mode == 2) {
+      for (int rr = 0; rr <= r; ++rr) visit(g.T + rr * g.F + c);
+    } else if (mode == 3) {
+      for (int rr = max(0, r - g.conv_half); rr <= r; ++rr)
+        for (int cc = max(0, c - g.conv_half); cc <= min(g.F - 1, c + g.conv_half); ++cc)
+          if (rr * g.F + cc <= p) visit(g.T + rr * g.F + cc);
+    } else {
+      for (int j = g.T; j <= pos; ++j) visit(j);
+    }
+  }
+  const float inv = 1.0f / l;
+  *reinterpret_cast<uint32_t*>(out + static_cast<long long>(b) * HD + h * 64 + lane * 2) = pack_bf16x2(a0 * inv, a1 * inv);
+}
+
+__device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+
+// One block (1024 threads) per sample: sort the n (<= 8192) logits descending (bitonic, in shared memory),
+// cut by top-k / top-p, draw one token.  Writes ids[b, pos + 1] = token + id_offset and codes[b, pos + 1 - T].
+constexpr int SAMPLE_MAX = 8192;
+__global__ void __launch_bounds__(1024)
+decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, float inv_temperature, int top_k,
+                     float top_p, unsigned long long seed, long long* __restrict__ ids, int ids_stride,
+                     long long id_offset, long long* __restrict__ codes, int codes_stride,
+                     const int* __restrict__ pos_ptr, int T) {
+  extern __shared__ unsigned long long skeys[];  // (ordered float bits << 32) | (0xffffffff - index)
+  __shared__ float sred[32];
+  __shared__ float sbc[2];
+  const int b = blockIdx.x, tid = threadIdx.x, pos = *pos_ptr;
+  const __nv_bfloat16* row = logits + static_cast<long long>(b) * ld;
+  int npow = 1;
+  while (npow < n) npow <<= 1;
+  for (int i = tid; i < npow; i += blockDim.x) {
+    unsigned long long key = 0ull;  // sorts last
+    if (i < n) {
+      const float x = __bfloat162float(row[i]) * inv_temperature;
+      uint32_t u = __float_as_uint(x);
+      u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // monotone map float -> uint
+      key = (static_cast<unsigned long long>(u) << 32) | (0xffffffffu - static_cast<uint32_t>(i));
+    }
+    skeys[i] = key;
+  }
+  __syncthreads();
+  for (int k = 2; k <= npow; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < npow; i += blockDim.x) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long a = skeys[i], c = skeys[ixj];
+          const bool desc = (i & k) == 0;  // descending overall
+          if (desc ? (a < c) : (a > c)) { skeys[i] = c; skeys[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  auto val = [&](int i) -> float {
+    uint32_t u = static_cast<uint32_t>(skeys[i] >> 32);
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    return __uint_as_float(u);
+  };
+  const float mx = val(0);
+  int keep = n;
+  if (top_k > 0 && top_k < keep) keep = top_k;
+  // total mass of the kept prefix (needed for the nucleus cut as well)
+  float s = 0.f;
+  for (int i = tid; i < keep; i += blockDim.x) s += __expf(val(i) - mx);  // mass after the top-k cut
+  s = warp_sum(s);
+  if ((tid & 31) == 0) sred[tid >> 5] = s;
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+    for (int i = 0; i < (blockDim.x >> 5); ++i) t += sred[i];
+    sbc[0] = t;
+  }
+  __syncthreads();
+  const float total = sbc[0];
+  if (tid == 0) {
+    // sequential walk over the sorted prefix: cheap (the nucleus is short) and exact
+    float cum = 0.f;
+    int cut = keep;
+    if (top_p < 1.0f) {
+      for (int i = 0; i < keep; ++i) {
+        const float p = __expf(val(i) - mx) / total;
+        if (cum > top_p) { cut = i; break; }  // keep tokens while the mass BEFORE them is <= top_p
+        cum += p;
+      }
+      if (cut < 1) cut = 1;
+    }
+    float kept = 0.f;
+    for (int i = 0; i < cut; ++i) kept += __expf(val(i) - mx);
+    const uint32_t r = hash_u32(static_cast<uint32_t>(seed) ^ hash_u32(static_cast<uint32_t>(seed >> 32) + 0x9e3779b9u * (pos + 1)) ^
+                                hash_u32(0x85ebca6bu * (b + 1)));
+    const float u = (static_cast<float>(r >> 8) + 0.5f) * (1.0f / 16777216.0f) * kept;
+    float acc = 0.f;
+    int pick = cut - 1;
+    for (int i = 0; i < cut; ++i) {
+      acc += __expf(val(i) - mx);
+      if (acc >= u) { pick = i; break; }
+    }
+    const long long tok = 0xffffffffu - static_cast<uint32_t>(skeys[pick] & 0xffffffffu);
+    ids[static_cast<long long>(b) * ids_stride + pos + 1] = tok + id_offset;
+    if (pos + 1 - T >= 0) codes[static_cast<long long>(b) * codes_stride + (pos + 1 - T)] = tok;
+  }
+}
+
+__global__ void decode_advance_kernel(int* pos_ptr) { *pos_ptr += 1; }
+
+static inline int derr() { return cudaGetLastError() == cudaSuccess ? 0 : -70; }
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_decode_embed(const long long* ids, int ids_stride, const float* W, float* x1, float* x2,
+                                 const int* pos_ptr, int B, int D, void* stream) {
+  decode_embed_kernel<<<(B * 32 + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(ids, ids_stride, W, x1,
+                                                                                               x2, pos_ptr, B, D);
+  return derr();
+}
+
+extern "C" int b200_decode_ln_shift(const float* x, const float* x2, const float* w, const float* bias, void* cache,
+                                    void* out, const int* pos_ptr, int B, int D, int seq, int T, int F, float eps,
+                                    int shift, void* stream) {
+  if (D % 128 || D > 1024) return -71;
+  DecGeom g{B, D, 0, seq, T, F, 0};
+  decode_ln_shift_kernel<<<(B * 32 + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, x2, w, bias, reinterpret_cast<__nv_bfloat16*>(cache), reinterpret_cast<__nv_bfloat16*>(out), pos_ptr, g, eps,
+      shift);
+  return derr();
+}
+
+extern "C" int b200_decode_attn(const void* qkv, void* kcache, void* vcache, void* out, const int* pos_ptr, int B,
+                                int H, int seq, int T, int F, int mode, int conv_kernel, void* stream) {
+  DecGeom g{B, H * 64, H, seq, T, F, conv_kernel / 2};
+  decode_attn_kernel<<<(B * H * 32 + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(kcache),
+      reinterpret_cast<__nv_bfloat16*>(vcache), reinterpret_cast<__nv_bfloat16*>(out), pos_ptr, g, mode);
+  return derr();
+}
+
+extern "C" int b200_decode_sample(const void* logits, int ld, int n, float temperature, int top_k, float top_p,
+                                  unsigned long long seed, long long* ids, int ids_stride, long long id_offset,
+                                  long long* codes, int codes_stride, const int* pos_ptr, int T, int B, void* stream) {
+  if (n > SAMPLE_MAX) return -72;
+  int npow = 1;
+  while (npow < n) npow <<= 1;
+  const size_t smem = static_cast<size_t>(npow) * sizeof(unsigned long long);
+  static bool configured = false;
+  if (!configured) {
+    if (cudaFuncSetAttribute(decode_sample_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             SAMPLE_MAX * (int)sizeof(unsigned long long)) != cudaSuccess)
+      return -73;
+    configured = true;
+  }
+  decode_sample_kernel<<<B, 1024, smem, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(logits), ld, n, 1.0f / fmaxf(temperature, 1e-6f), top_k, top_p, seed, ids,
+      ids_stride, id_offset, codes, codes_stride, pos_ptr, T);
+  return derr();
+}
+
+extern "C" int b200_decode_advance(int* pos_ptr, void* stream) {
+  decode_advance_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(pos_ptr);
+  return derr();
+}

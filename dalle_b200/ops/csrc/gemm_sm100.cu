@@ -42,6 +42,7 @@ struct GemmDev {
   const float2* rot;  // TRANSPOSED table [32 pairs][rot_len] of (cos, sin): lanes = consecutive rows -> coalesced
   int seq_len;
   int rot_len;
+  const int* pos_ptr;  // when set, every row uses this device-resident position (single-token decode)
   int q_cols;          // columns < q_cols are scaled by q_scale (rotary epilogue)
   float q_scale;
   const __nv_bfloat16* aux;  long long ldaux;
@@ -273,7 +274,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           } else if (EPI == B200_EPI_ROTARY) {
             // interleaved-pair rotary on q, k and v; q additionally scaled (dalle-pytorch applies
             // rotary to v as well)
-            const int pos = row % g.seq_len;
+            const int pos = g.pos_ptr ? __ldg(g.pos_ptr) : row % g.seq_len;
             const float2* rt = g.rot + (long long)((col & 63) >> 1) * g.rot_len + pos;
             const float s = (col < g.q_cols) ? g.q_scale : 1.0f;
             float o[32];
@@ -521,6 +522,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   g.res = d->res; g.ldres = d->ldres;
   g.rot = reinterpret_cast<const float2*>(d->rot); g.seq_len = d->seq_len > 0 ? d->seq_len : 1;
   g.rot_len = d->rot_len;
+  g.pos_ptr = reinterpret_cast<const int*>(d->pos_ptr);
   g.q_cols = d->q_cols; g.q_scale = d->q_scale;
   g.aux = reinterpret_cast<const __nv_bfloat16*>(d->aux); g.ldaux = d->ldaux;
   g.n_half = d->n_half;

@@ -109,7 +109,7 @@ def gemm_ref(mode, epi, A, B, out, *, out2=None, bias=None, scale=None, res=None
 
 def gemm(mode: int, epi: int, A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, out2=None, bias=None,
          scale=None, res=None, rot=None, seq_len: int = 0, q_cols: int = 0, q_scale: float = 1.0, aux=None,
-         n_half: int = 0, alpha: float = 1.0, splits: int = 0):
+         n_half: int = 0, alpha: float = 1.0, splits: int = 0, pos_ptr=None):
     """out = epilogue(A (x) B).  Shapes by mode: NT A[M,K] B[N,K]; NN A[M,K] B[K,N]; TN A[K,M] B[K,N]."""
     if not A.is_cuda:
         return gemm_ref(mode, epi, A, B, out, out2=out2, bias=bias, scale=scale, res=res, rot=rot, seq_len=seq_len,
@@ -141,6 +141,7 @@ def gemm(mode: int, epi: int, A: torch.Tensor, B: torch.Tensor, out: torch.Tenso
         rot_t = rot_transposed(rot)
         d.rot, d.rot_len = rot_t.data_ptr(), rot_t.shape[1]
     d.seq_len, d.q_cols, d.q_scale = seq_len, q_cols, q_scale
+    d.pos_ptr = _ptr(pos_ptr)
     d.aux, d.ldaux = _ptr(aux), _ld(aux)
     d.n_half, d.alpha, d.splits = n_half, alpha, splits
     rc = lib.cuda_lib().b200_gemm_bf16(ctypes.byref(d), torch.cuda.current_stream().cuda_stream)

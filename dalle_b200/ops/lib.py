@@ -28,6 +28,7 @@ class B200Gemm(ctypes.Structure):
         ("res", ctypes.c_void_p), ("ldres", ctypes.c_longlong),
         ("rot", ctypes.c_void_p),
         ("seq_len", ctypes.c_int), ("rot_len", ctypes.c_int), ("q_cols", ctypes.c_int), ("q_scale", ctypes.c_float),
+        ("pos_ptr", ctypes.c_void_p),
         ("aux", ctypes.c_void_p), ("ldaux", ctypes.c_longlong),
         ("n_half", ctypes.c_int), ("alpha", ctypes.c_float), ("splits", ctypes.c_int),
     ]
@@ -124,6 +125,11 @@ class _Sigs:
     b200_cast_f32_bf16 = [_p, _p, _l, _p]
     b200_lamb_step = [_p, _p, _p, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _p, _i, _p, _p,
                       _f, _f, _f, _f, _f, _f, _f, _i, _p]
+    b200_decode_embed = [_p, _i, _p, _p, _p, _p, _i, _i, _p]
+    b200_decode_ln_shift = [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _f, _i, _p]
+    b200_decode_attn = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
+    b200_decode_sample = [_p, _i, _i, _f, _i, _f, ctypes.c_ulonglong, _p, _i, _l, _p, _i, _p, _i, _i, _p]
+    b200_decode_advance = [_p, _p]
     b200_attn_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _i, _i, _i, _i, _p]
 
 

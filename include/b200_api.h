@@ -45,6 +45,7 @@ typedef struct B200Gemm {
   const float* res; long long ldres; /* fp32 residual (RESID) */
   const void* rot;     /* float2[32][rot_len] = (cos, sin) per interleaved pair, pair-major (ROTARY) */
   int seq_len; int rot_len; int q_cols; float q_scale;
+  const void* pos_ptr; /* optional device int: one position for all rows (decode) */
   const void* aux; long long ldaux; /* bf16 [M, 2*n_half] (GEGLU_BWD) */
   int n_half;          /* GEGLU: N counts value columns only; B has 2*n_half rows */
   float alpha;
@@ -139,6 +140,22 @@ typedef struct B200Group {
   float beta1, beta2, eps, max_grad_norm, clamp_value, lr, grad_scale;
 } B200Group;
 int b200_group_lamb_step(const B200Group* desc, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Single-token decode kernels (decode.cu) for KV-cached image sampling; every kernel reads the current position
+ * from device memory (pos_ptr) so a whole decode step can be captured in a CUDA graph.  Replaces the cached
+ * forward + sampling loop of dalle-pytorch generate_images (reference inference/run_inference.py:87-91).
+ * ---------------------------------------------------------------------------------------------- */
+int b200_decode_embed(const long long* ids, int ids_stride, const float* W, float* x1, float* x2, const int* pos_ptr,
+                      int B, int D, void* stream);
+int b200_decode_ln_shift(const float* x, const float* x2, const float* w, const float* bias, void* cache, void* out,
+                         const int* pos_ptr, int B, int D, int seq, int T, int F, float eps, int shift, void* stream);
+int b200_decode_attn(const void* qkv, void* kcache, void* vcache, void* out, const int* pos_ptr, int B, int H, int seq,
+                     int T, int F, int mode, int conv_kernel, void* stream);
+int b200_decode_sample(const void* logits, int ld, int n, float temperature, int top_k, float top_p,
+                       unsigned long long seed, long long* ids, int ids_stride, long long id_offset, long long* codes,
+                       int codes_stride, const int* pos_ptr, int T, int B, void* stream);
+int b200_decode_advance(int* pos_ptr, void* stream);
 
 /* b200_lamb_step for callers that cannot provide scratch memory.  No counterpart in the reference: it exists for
  * embedders of this library that may not allocate device memory once they are running (all of it belongs to their
