@@ -32,6 +32,15 @@ from ..transport.p2p import P2PError, PeerID, Stream
 from . import compression as C
 
 
+def _bulk_available() -> bool:
+    try:
+        from ..transport import bulk
+
+        return bulk.available()
+    except Exception:
+        return False
+
+
 class AveragingMode(enum.IntEnum):
     NODE = 0      # owns a span and contributes data
     CLIENT = 1    # contributes data, cannot accept connections (owns nothing)
@@ -564,7 +573,33 @@ class DecentralizedAverager:
             if not self.allow_state_sharing:
                 await stream.send({"err": "state sharing disabled"})
                 return
-            meta, tensors = await asyncio.get_event_loop().run_in_executor(None, self.get_current_state)
+            loop = asyncio.get_event_loop()
+            meta, tensors = await loop.run_in_executor(None, self.get_current_state)
+            use_bulk = bool(payload and payload.get("bulk")) and _bulk_available() and \
+                isinstance(self.state_compression, C.NoCompression)
+            if use_bulk:
+                # tensors travel over the C++ bulk transport (raw frames, GIL released); control stays here
+                from ..transport.bulk import BulkListener
+
+                lst = BulkListener(self.dht.p2p.endpoint[0] if self.dht.p2p.endpoint else "127.0.0.1", 0)
+                await stream.send({"meta": msgpack.packb(meta, use_bin_type=True), "n": len(tensors),
+                                   "bulk_port": lst.port, "shapes": [list(t.shape) for t in tensors],
+                                   "dtypes": [str(t.dtype) for t in tensors]})
+
+                def serve():
+                    conn = lst.accept(self.request_timeout * 3)
+                    try:
+                        if conn is not None:
+                            for i, t in enumerate(tensors):
+                                conn.send_tensor(t, tag=i)
+                    finally:
+                        if conn is not None:
+                            conn.close()
+                        lst.close()
+
+                await loop.run_in_executor(None, serve)
+                await stream.send({"done": 1})
+                return
             await stream.send({"meta": msgpack.packb(meta, use_bin_type=True), "n": len(tensors)})
             for i, t in enumerate(tensors):
                 flat = t.reshape(-1)
@@ -592,12 +627,30 @@ class DecentralizedAverager:
                          if bytes(pid) != me and v.value), reverse=True)
         for prio, pid, ep in donors:
             try:
-                stream = await self.dht.p2p.open_stream(ep, f"{self.prefix}.download", None, timeout=self.request_timeout)
+                stream = await self.dht.p2p.open_stream(ep, f"{self.prefix}.download", {"bulk": _bulk_available()},
+                                                        timeout=self.request_timeout)
                 try:
                     head = await stream.recv(timeout or 30.0)
                     if "err" in head:
                         continue
                     meta = msgpack.unpackb(head["meta"], raw=False, strict_map_key=False)
+                    if "bulk_port" in head:
+                        from ..transport.bulk import BulkConnection
+
+                        def fetch():
+                            conn = BulkConnection.connect((ep[0], head["bulk_port"]), self.request_timeout)
+                            try:
+                                out = []
+                                for shape, dt in zip(head["shapes"], head["dtypes"]):
+                                    t = torch.empty(shape, dtype=getattr(torch, dt.replace("torch.", "")))
+                                    conn.recv_into(t, timeout or 60.0)
+                                    out.append(t)
+                                return out
+                            finally:
+                                conn.close()
+
+                        tensors = await asyncio.get_event_loop().run_in_executor(None, fetch)
+                        return meta, tensors
                     chunks: Dict[int, list] = {}
                     shapes: Dict[int, list] = {}
                     while True:
