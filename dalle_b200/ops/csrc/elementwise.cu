@@ -115,22 +115,27 @@ __global__ void ln_shift_apply_kernel(const float* __restrict__ x, const float* 
 // transposed shift; dx = rstd * (w*dn - mean(w*dn) - xhat * mean(w*dn*xhat)).
 //   mode 0: dx_out[t] += dx           (reversible block: accumulate into the running stream gradient)
 //   mode 1: dx_out[t] = dx2_out[t] = 0.5 * dx   (final norm over the mean of the two streams)
-// Row kernel (one warp per row, high occupancy) + column kernel for dw += dn*xhat, db += dn.
+// Row kernel (4 warps per row -> 8 elements per thread, full occupancy) + column kernel for dw, db.
 __global__ void __launch_bounds__(256)
 ln_shift_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
                        const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
                        float* __restrict__ dx_out, float* __restrict__ dx2_out, int M, int D, ShiftGeom sg, int mode) {
-  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (row >= M) return;
-  const int nv = D / 128;
-  const int bidx = row / sg.seq, t = row - bidx * sg.seq;
-  const float mu = mean[row], rs = rstd[row];
-  float4 dn[MAXV], xh[MAXV];
+  __shared__ float sred[2][4][2];
+  const int sub = threadIdx.x >> 7;            // which of the block's 2 rows
+  const int t128 = threadIdx.x & 127;          // thread inside the row group
+  const int wsub = t128 >> 5;                  // warp inside the row group
+  const int row = blockIdx.x * 2 + sub;
+  const bool live = row < M;
+  const int nper = D / 512;                    // float4 chunks per thread (D = 1024 -> 2, D = 512 -> 1)
+  const int rrow = live ? row : 0;
+  const int bidx = rrow / sg.seq, t = rrow - bidx * sg.seq;
+  const float mu = mean[rrow], rs = rstd[rrow];
+  float4 dn[2], xh[2];
   float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-  for (int k = 0; k < MAXV; ++k) {
-    if (k < nv) {
-      const int col = k * 128 + lane * 4;
+  for (int k = 0; k < 2; ++k) {
+    const int col = k * 512 + t128 * 4;
+    if (k < nper || (nper == 0 && k == 0 && col < D)) {
       const int dt = shift_dst(sg, t, col, D);
       float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
       if (dt >= 0) {
@@ -138,9 +143,9 @@ ln_shift_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dh, const float* __rest
         const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
         g = make_float4(a.x, a.y, c.x, c.y);
       }
-      float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
+      float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(rrow) * D + col);
       if (x2) {
-        const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
+        const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(rrow) * D + col);
         v.x = 0.5f * (v.x + u2.x); v.y = 0.5f * (v.y + u2.y); v.z = 0.5f * (v.z + u2.z); v.w = 0.5f * (v.w + u2.w);
       }
       const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
@@ -148,14 +153,21 @@ ln_shift_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dh, const float* __rest
       dn[k] = make_float4(g.x * ww.x, g.y * ww.y, g.z * ww.z, g.w * ww.w);
       s1 += dn[k].x + dn[k].y + dn[k].z + dn[k].w;
       s2 += dn[k].x * xh[k].x + dn[k].y * xh[k].y + dn[k].z * xh[k].z + dn[k].w * xh[k].w;
+    } else {
+      dn[k] = xh[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
-  s1 = warp_sum(s1) / D;
-  s2 = warp_sum(s2) / D;
+  s1 = warp_sum(s1);
+  s2 = warp_sum(s2);
+  if ((threadIdx.x & 31) == 0) { sred[sub][wsub][0] = s1; sred[sub][wsub][1] = s2; }
+  __syncthreads();
+  s1 = (sred[sub][0][0] + sred[sub][1][0] + sred[sub][2][0] + sred[sub][3][0]) / D;
+  s2 = (sred[sub][0][1] + sred[sub][1][1] + sred[sub][2][1] + sred[sub][3][1]) / D;
+  if (!live) return;
 #pragma unroll
-  for (int k = 0; k < MAXV; ++k) {
-    if (k < nv) {
-      const int col = k * 128 + lane * 4;
+  for (int k = 0; k < 2; ++k) {
+    const int col = k * 512 + t128 * 4;
+    if (k < nper || (nper == 0 && k == 0 && col < D)) {
       float4 d;
       d.x = rs * (dn[k].x - s1 - xh[k].x * s2);
       d.y = rs * (dn[k].y - s1 - xh[k].y * s2);
@@ -174,7 +186,7 @@ ln_shift_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dh, const float* __rest
   }
 }
 
-// dw[col] += sum_rows dn*xhat ; db[col] += sum_rows dn.  thread = 4 columns, block = one row slice.
+// dw[col] += sum_rows dn*xhat ; db[col] += sum_rows dn.  thread = 4 columns, block = one row slice; 4 rows in flight.
 __global__ void __launch_bounds__(256)
 ln_shift_bwd_dwdb_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x,
                          const float* __restrict__ x2, const float* __restrict__ mean, const float* __restrict__ rstd,
@@ -186,23 +198,43 @@ ln_shift_bwd_dwdb_kernel(const __nv_bfloat16* __restrict__ dh, const float* __re
   const int rows_per = (M + nsplit - 1) / nsplit;
   const int r0 = rsplit * rows_per, r1 = min(M, r0 + rows_per);
   float4 aw = make_float4(0.f, 0.f, 0.f, 0.f), ab = make_float4(0.f, 0.f, 0.f, 0.f);
-  int bidx = r0 / sg.seq, t = r0 - bidx * sg.seq;
-  for (int row = r0; row < r1; ++row) {
-    const int dt = shift_dst(sg, t, col, D);
-    if (dt >= 0) {
-      const uint2 u = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
-      const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
-      float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
-      if (x2) {
-        const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
-        v.x = 0.5f * (v.x + u2.x); v.y = 0.5f * (v.y + u2.y); v.z = 0.5f * (v.z + u2.z); v.w = 0.5f * (v.w + u2.w);
+  for (int base = r0; base < r1; base += 4) {
+    uint2 u[4];
+    float4 v[4];
+    float mu[4], rs[4];
+    bool ok[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int row = base + j;
+      ok[j] = false;
+      u[j] = make_uint2(0u, 0u);
+      v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      mu[j] = 0.f; rs[j] = 0.f;
+      if (row < r1) {
+        const int bidx = row / sg.seq, t = row - bidx * sg.seq;
+        const int dt = shift_dst(sg, t, col, D);
+        if (dt >= 0) {
+          ok[j] = true;
+          u[j] = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
+          v[j] = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
+          if (x2) {
+            const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
+            v[j] = make_float4(0.5f * (v[j].x + u2.x), 0.5f * (v[j].y + u2.y), 0.5f * (v[j].z + u2.z), 0.5f * (v[j].w + u2.w));
+          }
+          mu[j] = mean[row];
+          rs[j] = rstd[row];
+        }
       }
-      const float mu = mean[row], rs = rstd[row];
-      aw.x += a.x * (v.x - mu) * rs; aw.y += a.y * (v.y - mu) * rs;
-      aw.z += c.x * (v.z - mu) * rs; aw.w += c.y * (v.w - mu) * rs;
-      ab.x += a.x; ab.y += a.y; ab.z += c.x; ab.w += c.y;
     }
-    if (++t == sg.seq) { t = 0; ++bidx; }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (ok[j]) {
+        const float2 a = unpack_bf16x2(u[j].x), c = unpack_bf16x2(u[j].y);
+        aw.x += a.x * (v[j].x - mu[j]) * rs[j]; aw.y += a.y * (v[j].y - mu[j]) * rs[j];
+        aw.z += c.x * (v[j].z - mu[j]) * rs[j]; aw.w += c.y * (v[j].w - mu[j]) * rs[j];
+        ab.x += a.x; ab.y += a.y; ab.z += c.x; ab.w += c.y;
+      }
+    }
   }
   atomicAdd(dw + col, aw.x); atomicAdd(dw + col + 1, aw.y); atomicAdd(dw + col + 2, aw.z); atomicAdd(dw + col + 3, aw.w);
   atomicAdd(db + col, ab.x); atomicAdd(db + col + 1, ab.y); atomicAdd(db + col + 2, ab.z); atomicAdd(db + col + 3, ab.w);
@@ -419,8 +451,9 @@ extern "C" int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2
   if (D % 128 || D > 128 * MAXV) return -41;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
-  const int threads = 256, rows_per_block = threads / 32;
-  const int blocks = (M + rows_per_block - 1) / rows_per_block;
+  if (D % 512 && D != 256) return -41;  // 4 warps per row: D in {256, 512, 1024}
+  const int threads = 256;
+  const int blocks = (M + 1) / 2;
   ln_shift_bwd_dx_kernel<<<blocks, threads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2, mean, rstd, w,
                                                      dx, dx2, M, D, sg, mode);
   int cthreads = 256;

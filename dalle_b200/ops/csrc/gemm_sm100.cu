@@ -21,12 +21,20 @@ namespace b200 {
 constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;
-constexpr int STAGES = 4;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int GEMM_THREADS = 320;  // TMA warp + MMA warp + 8 epilogue warps
-constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64B-swizzled TMA-store box
+constexpr int OUT_TILES_PER_WARP = 3;
+constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
+__host__ __device__ constexpr int gemm_stages(int epi) { return epi == B200_EPI_GEGLU ? 3 : 4; }
+__host__ __device__ constexpr int gemm_out_stage_bytes(int epi) {
+  return epi == B200_EPI_GEGLU ? OUT_STAGE_BYTES : (OUT_STAGE_BYTES * 2) / 3;  // 3 tiles/warp only for GEGLU
+}
+__host__ __device__ constexpr int gemm_smem_bytes(int epi) {
+  return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 256 /*barriers*/;
+}
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 
 struct GemmDev {
@@ -92,14 +100,17 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* rowp, int col, int
 
 template <int A_MN, int B_MN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmDev g) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const GemmDev g) {
+  constexpr int STAGES = gemm_stages(EPI);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t pad = ((raw_addr + 1023u) & ~1023u) - raw_addr;
   uint8_t* smem = smem_raw + pad;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * A_STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint8_t* smem_out = smem + STAGES * STAGE_BYTES;  // per-warp staging tiles for TMA stores (1024-aligned)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES + gemm_out_stage_bytes(EPI));
   uint64_t* full_bar = bars;                 // [STAGES]
   uint64_t* empty_bar = bars + STAGES;       // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
@@ -210,6 +221,33 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ------------------------------- epilogue warps -------------------------------------------
     const int q = warp & 3;
     const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
+    constexpr int TILES = (EPI == B200_EPI_GEGLU) ? 3 : 2;
+    uint8_t* stage = smem_out + (warp - 2) * TILES * OUT_TILE_BYTES;
+    // bf16 outputs leave through smem: 32 rows x 32 columns per warp and chunk, 64B-swizzled, one TMA store each
+    // (full 32-byte sectors instead of 32 scattered 16-byte row pieces per store instruction)
+    auto stage_write = [&](int tile, const float* v32) {
+      uint8_t* base = stage + tile * OUT_TILE_BYTES + lane * 64;
+      const int sw = (lane >> 1) & 3;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        uint4 u;
+        u.x = pack_bf16x2(v32[8 * p + 0], v32[8 * p + 1]);
+        u.y = pack_bf16x2(v32[8 * p + 2], v32[8 * p + 3]);
+        u.z = pack_bf16x2(v32[8 * p + 4], v32[8 * p + 5]);
+        u.w = pack_bf16x2(v32[8 * p + 6], v32[8 * p + 7]);
+        *reinterpret_cast<uint4*>(base + ((p ^ sw) << 4)) = u;
+      }
+    };
+    auto stage_reuse = [&]() {  // the previous chunk's stores must have read the staging tiles
+      if (lane == 0) tma_store_wait_read();
+      __syncwarp();
+    };
+    auto stage_flush = [&](const CUtensorMap* m, int tile, int x, int y) {
+      if (lane == 0) tma_store_2d(m, stage + tile * OUT_TILE_BYTES, x, y);
+    };
+    auto stage_commit = [&]() {
+      if (lane == 0) tma_store_commit();
+    };
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -231,20 +269,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tmem_ld32(taddr + 128 + c * 32, rg);
           tmem_ld_wait();
           const int col = n0 + c * 32;
-          if (row_ok && col < g.n_half) {
+          if (col < g.n_half) {  // warp-uniform
             float va[32], vg[32], o[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              va[j] = __uint_as_float(ra[j]) + (g.bias ? __ldg(g.bias + col + j) : 0.f);
-              vg[j] = __uint_as_float(rg[j]) + (g.bias ? __ldg(g.bias + g.n_half + col + j) : 0.f);
+              const bool cok = col + j < g.n_half;
+              va[j] = __uint_as_float(ra[j]) + ((g.bias && cok) ? __ldg(g.bias + col + j) : 0.f);
+              vg[j] = __uint_as_float(rg[j]) + ((g.bias && cok) ? __ldg(g.bias + g.n_half + col + j) : 0.f);
               o[j] = va[j] * gelu_erf(vg[j]);
             }
-            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo, col, g.n_half, o);
-            if (g.out2) {
-              __nv_bfloat16* p2 = reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2;
-              store_row_bf16(p2, col, g.n_half, va);
-              store_row_bf16(p2 + g.n_half, col, g.n_half, vg);
-            }
+            const int y = m_blk * BM + q * 32;
+            stage_reuse();
+            stage_write(0, o);
+            if (g.out2) { stage_write(1, va); stage_write(2, vg); }
+            fence_proxy_async_smem();
+            __syncwarp();
+            stage_flush(&tmO, 0, col, y);
+            if (g.out2) { stage_flush(&tmO2, 1, col, y); stage_flush(&tmO2, 2, g.n_half + col, y); }
+            stage_commit();
           }
         }
       } else {
@@ -255,7 +297,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint32_t r[32];
           tmem_ld32(taddr + c * 32, r);
           tmem_ld_wait();
-          if (!row_ok) continue;
+          constexpr bool kStaged = (EPI == B200_EPI_BF16 || EPI == B200_EPI_ROTARY || EPI == B200_EPI_GEGLU_BWD);
+          if (!kStaged && !row_ok) continue;   // staged epilogues keep the warp converged; TMA clips the tails
+          const int y = m_blk * BM + q * 32;
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
@@ -270,7 +314,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] *= g.alpha;
             }
-            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo, col, g.N, v);
+            stage_reuse();
+            stage_write(0, v);
+            fence_proxy_async_smem();
+            __syncwarp();
+            stage_flush(&tmO, 0, col, y);
+            stage_commit();
           } else if (EPI == B200_EPI_ROTARY) {
             // interleaved-pair rotary on q, k and v; q additionally scaled (dalle-pytorch applies
             // rotary to v as well)
@@ -281,12 +330,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
             for (int j = 0; j < 32; j += 2) {
               const float2 cs = __ldg(rt + (long long)(j >> 1) * g.rot_len);
-              const float x0 = v[j] + (g.bias ? __ldg(g.bias + col + j) : 0.f);
-              const float x1 = v[j + 1] + (g.bias ? __ldg(g.bias + col + j + 1) : 0.f);
+              const float x0 = v[j] + ((g.bias && col + j < g.N) ? __ldg(g.bias + col + j) : 0.f);
+              const float x1 = v[j + 1] + ((g.bias && col + j + 1 < g.N) ? __ldg(g.bias + col + j + 1) : 0.f);
               o[j] = (x0 * cs.x - x1 * cs.y) * s;
               o[j + 1] = (x1 * cs.x + x0 * cs.y) * s;
             }
-            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo, col, g.N, o);
+            stage_reuse();
+            stage_write(0, o);
+            fence_proxy_async_smem();
+            __syncwarp();
+            stage_flush(&tmO, 0, col, y);
+            stage_commit();
           } else if (EPI == B200_EPI_RESID) {
             // out = res + alpha * scale[col] * (acc + bias[col]); optional bf16 copy of (acc + bias)
             float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
@@ -318,9 +372,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (g.out2)
               store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2, col, g.N, v);
           } else if (EPI == B200_EPI_GEGLU_BWD) {
+            if (!row_ok) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = 0.f;
+            }
             // acc = d(geglu out); aux = [value_pre | gate_pre] (bf16, ld = ldaux)
-            const __nv_bfloat16* ap = g.aux + (long long)row * g.ldaux + col;
-            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(g.out) + (long long)row * g.ldo;
+            const __nv_bfloat16* ap = g.aux + (long long)(row_ok ? row : 0) * g.ldaux + col;
             float da[32], dg[32];
             if (full) {
 #pragma unroll
@@ -346,8 +403,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 }
               }
             }
-            store_row_bf16(op, col, g.N, da);
-            store_row_bf16(op + g.n_half, col, g.N, dg);
+            stage_reuse();
+            stage_write(0, da);
+            stage_write(1, dg);
+            fence_proxy_async_smem();
+            __syncwarp();
+            stage_flush(&tmO, 0, col, y);
+            stage_flush(&tmO, 1, g.n_half + col, y);
+            stage_commit();
           } else if (EPI == B200_EPI_ATOMIC_F32) {
             float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
             if (full) {
@@ -379,6 +442,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    if (lane == 0) tma_store_wait_all();  // staged stores must finish before the CTA's smem goes away
   }
 
   tc_fence_before();
@@ -424,6 +488,20 @@ int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t c
   return r == CUDA_SUCCESS ? 0 : -2;
 }
 
+// Output-side map for the staged epilogue: box {32 columns, 32 rows}, 64-byte swizzle.
+int make_tmap_bf16_out(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -1;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 2};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
 int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                       const uint32_t* box) {
   EncodeTiledFn fn = get_encode_fn();
@@ -450,16 +528,19 @@ int num_sms() {
   return n;
 }
 
+static CUtensorMap g_tm_out, g_tm_out2;  // set by b200_gemm_bf16 before launch<>() (host-side, per call)
+
 template <int A_MN, int B_MN, int EPI>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
   auto kern = gemm_kernel<A_MN, B_MN, EPI>;
+  constexpr int smem = gemm_smem_bytes(EPI);
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return -3;
     configured = true;
   }
-  kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, st>>>(ta, tb, g);
+  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g);
   return cudaGetLastError() == cudaSuccess ? 0 : -4;
 }
 
@@ -528,6 +609,25 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   g.n_half = d->n_half;
   g.alpha = d->alpha;
 
+  // output maps for the TMA-store epilogues
+  g_tm_out = ta;
+  g_tm_out2 = ta;  // placeholders when unused
+  {
+    const bool staged = d->epi == B200_EPI_BF16 || d->epi == B200_EPI_ROTARY || d->epi == B200_EPI_GEGLU ||
+                        d->epi == B200_EPI_GEGLU_BWD;
+    if (staged) {
+      if ((d->ldo % 8) || reinterpret_cast<uintptr_t>(d->out) % 16) return -15;
+      const uint64_t ocols = d->epi == B200_EPI_GEGLU ? (uint64_t)d->n_half
+                             : (d->epi == B200_EPI_GEGLU_BWD ? (uint64_t)2 * d->n_half : (uint64_t)d->N);
+      rc = make_tmap_bf16_out(&g_tm_out, d->out, d->M, ocols, d->ldo);
+      if (rc) return rc;
+      if (d->epi == B200_EPI_GEGLU && d->out2) {
+        if ((d->ldo2 % 8) || reinterpret_cast<uintptr_t>(d->out2) % 16) return -15;
+        rc = make_tmap_bf16_out(&g_tm_out2, d->out2, d->M, (uint64_t)2 * d->n_half, d->ldo2);
+        if (rc) return rc;
+      }
+    }
+  }
   const int units = tiles * splits;
   const int grid = units < num_sms() ? units : num_sms();
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
