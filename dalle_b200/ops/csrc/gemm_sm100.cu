@@ -58,12 +58,25 @@ struct GemmDev {
   float alpha;
 };
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
-__device__ __forceinline__ float gelu_erf_grad(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+// erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7): one exp + one reciprocal, and the same exp(-x^2) is the
+// Gaussian pdf factor the GELU derivative needs.
+struct GeluParts { float cdf, pdf; };
+__device__ __forceinline__ GeluParts gelu_parts(float g) {
+  const float x = fabsf(g) * 0.70710678118654752f;
+  const float e = __expf(-x * x);                       // = exp(-g^2 / 2)
+  const float t = __frcp_rn(fmaf(0.3275911f, x, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float erf_abs = 1.0f - poly * t * e;
+  const float erf_v = copysignf(erf_abs, g);
+  GeluParts r;
+  r.cdf = 0.5f * (1.0f + erf_v);
+  r.pdf = 0.3989422804014327f * e;
+  return r;
 }
+__device__ __forceinline__ float gelu_erf(float x) { return x * gelu_parts(x).cdf; }
 
 __device__ __forceinline__ void st_bf16x8(__nv_bfloat16* p, const float* v) {
   uint4 u;
@@ -387,8 +400,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                 ld_bf16x8(ap + g.n_half + j, g8);
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
-                  da[j + e] = v[j + e] * gelu_erf(g8[e]);
-                  dg[j + e] = v[j + e] * a8[e] * gelu_erf_grad(g8[e]);
+                  const GeluParts gp = gelu_parts(g8[e]);
+                  da[j + e] = v[j + e] * g8[e] * gp.cdf;
+                  dg[j + e] = v[j + e] * a8[e] * fmaf(g8[e], gp.pdf, gp.cdf);
                 }
               }
             } else {
@@ -396,8 +410,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               for (int j = 0; j < 32; ++j) {
                 if (col + j < g.N) {
                   const float a = __bfloat162float(ap[j]), gg = __bfloat162float(ap[g.n_half + j]);
-                  da[j] = v[j] * gelu_erf(gg);
-                  dg[j] = v[j] * a * gelu_erf_grad(gg);
+                  const GeluParts gp = gelu_parts(gg);
+                  da[j] = v[j] * gg * gp.cdf;
+                  dg[j] = v[j] * a * fmaf(gg, gp.pdf, gp.cdf);
                 } else {
                   da[j] = dg[j] = 0.f;
                 }
