@@ -35,6 +35,7 @@ class DecodeEngine:
         self.ids = z(B, n + 1, dtype=torch.int64)
         self.codes = z(B, cfg.image_seq_len, dtype=torch.int64)
         self.pos = z(1, dtype=torch.int32)
+        self.seed = z(1, dtype=torch.int64)
         self.dummy_mean, self.dummy = z(B, dtype=torch.float32), None
         self._graphs = {}
         self._sampling = None
@@ -43,7 +44,7 @@ class DecodeEngine:
         self._w = model.engine.w if model._engine is not None else Engine(model).w
 
     # ---- one decode step (enqueued on the current stream) ------------------------------------------
-    def _step(self, with_head: bool, temperature: float, top_k: int, top_p: float, seed: int):
+    def _step(self, with_head: bool, temperature: float, top_k: int, top_p: float):
         m, cfg, L = self.model, self.cfg, lib.cuda_lib()
         st = torch.cuda.current_stream().cuda_stream
         B, D, I = self.batch, cfg.dim, cfg.inner_dim
@@ -77,22 +78,25 @@ class DecodeEngine:
             v0, nv = cfg.total_text_tokens, cfg.num_image_tokens
             G.gemm(G.NT, G.EPI_BF16, self.hf, self._w(m.emb_weight)[v0:v0 + nv], self.logits[:, :nv],
                    bias=m.emb_bias.detach()[v0:v0 + nv])
-            ck(L.b200_decode_sample(self.logits.data_ptr(), self.ld, nv, temperature, top_k, top_p, seed,
+            ck(L.b200_decode_sample(self.logits.data_ptr(), self.ld, nv, temperature, top_k, top_p, self.seed.data_ptr(),
                                     self.ids.data_ptr(), self.ids.shape[1], v0, self.codes.data_ptr(),
                                     self.codes.shape[1], pp, cfg.text_len, B, st), "decode_sample")
         ck(L.b200_decode_advance(pp, st), "decode_advance")
 
-    def _graph(self, with_head: bool, temperature, top_k, top_p, seed):
-        key = (with_head, float(temperature), int(top_k), float(top_p), int(seed))
+    def _graph(self, with_head: bool, temperature, top_k, top_p):
+        key = (with_head, float(temperature), int(top_k), float(top_p))
         g = self._graphs.get(key)
         if g is None:
-            # warm-up outside capture (function attributes, lazy module loading), then capture
+            # warm-up outside capture (function attributes, lazy module loading), then capture.  Both run one
+            # real decode step, so the position must be a valid one.
+            self.pos.zero_()
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):
                 self._step(*key[:1], *key[1:])
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
+            self.pos.zero_()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self._step(*key[:1], *key[1:])
@@ -110,18 +114,18 @@ class DecodeEngine:
         seed = int(generator.initial_seed()) if generator is not None else int(torch.seed() & 0x7FFFFFFFFFFFFFFF)
         T = cfg.text_len
         if use_graph:
-            g_body = self._graph(False, 1.0, 0, 1.0, 0)
-            g_full = self._graph(True, temperature, top_k, top_p, seed)
+            g_body = self._graph(False, 1.0, 0, 1.0)
+            g_full = self._graph(True, temperature, top_k, top_p)
         # (graph construction ran warm-up steps: reset the state afterwards)
         self.ids.zero_()
         self.ids[:, 1:T] = text
         self.pos.zero_()
         self.codes.zero_()
-        n0 = lib.launch_count
+        self.seed.fill_(seed)
         for pos in range(cfg.seq_len):
             head = pos >= T - 1
             if use_graph:
                 (g_full if head else g_body).replay()
             else:
-                self._step(head, temperature, top_k, top_p, seed)
+                self._step(head, temperature, top_k, top_p)
         return self.codes.clone()

@@ -161,7 +161,7 @@ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
 constexpr int SAMPLE_MAX = 8192;
 __global__ void __launch_bounds__(1024)
 decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, float inv_temperature, int top_k,
-                     float top_p, unsigned long long seed, long long* __restrict__ ids, int ids_stride,
+                     float top_p, const unsigned long long* __restrict__ seed_ptr, long long* __restrict__ ids, int ids_stride,
                      long long id_offset, long long* __restrict__ codes, int codes_stride,
                      const int* __restrict__ pos_ptr, int T) {
   extern __shared__ unsigned long long skeys[];  // (ordered float bits << 32) | (0xffffffff - index)
@@ -230,6 +230,7 @@ decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, fl
     }
     float kept = 0.f;
     for (int i = 0; i < cut; ++i) kept += __expf(val(i) - mx);
+    const unsigned long long seed = *seed_ptr;
     const uint32_t r = hash_u32(static_cast<uint32_t>(seed) ^ hash_u32(static_cast<uint32_t>(seed >> 32) + 0x9e3779b9u * (pos + 1)) ^
                                 hash_u32(0x85ebca6bu * (b + 1)));
     const float u = (static_cast<float>(r >> 8) + 0.5f) * (1.0f / 16777216.0f) * kept;
@@ -281,7 +282,7 @@ extern "C" int b200_decode_attn(const void* qkv, void* kcache, void* vcache, voi
 }
 
 extern "C" int b200_decode_sample(const void* logits, int ld, int n, float temperature, int top_k, float top_p,
-                                  unsigned long long seed, long long* ids, int ids_stride, long long id_offset,
+                                  const unsigned long long* seed, long long* ids, int ids_stride, long long id_offset,
                                   long long* codes, int codes_stride, const int* pos_ptr, int T, int B, void* stream) {
   if (n > SAMPLE_MAX) return -72;
   int npow = 1;

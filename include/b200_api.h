@@ -153,7 +153,8 @@ int b200_decode_ln_shift(const float* x, const float* x2, const float* w, const 
 int b200_decode_attn(const void* qkv, void* kcache, void* vcache, void* out, const int* pos_ptr, int B, int H, int seq,
                      int T, int F, int mode, int conv_kernel, void* stream);
 int b200_decode_sample(const void* logits, int ld, int n, float temperature, int top_k, float top_p,
-                       unsigned long long seed, long long* ids, int ids_stride, long long id_offset, long long* codes,
+                       const unsigned long long* seed /* device */, long long* ids, int ids_stride, long long id_offset,
+                       long long* codes,
                        int codes_stride, const int* pos_ptr, int T, int B, void* stream);
 int b200_decode_advance(int* pos_ptr, void* stream);
 

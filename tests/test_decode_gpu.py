@@ -50,7 +50,8 @@ def test_sampler_distribution():
     codes = torch.zeros(trials, 8, dtype=torch.int64, device="cuda")
     pos = torch.zeros(1, dtype=torch.int32, device="cuda")
     L = lib.cuda_lib()
-    rc = L.b200_decode_sample(logits.data_ptr(), 512, n, 1.0, 0, 1.0, 1234, ids.data_ptr(), 8, 1000, codes.data_ptr(),
+    seed = torch.tensor([1234], dtype=torch.int64, device="cuda")
+    rc = L.b200_decode_sample(logits.data_ptr(), 512, n, 1.0, 0, 1.0, seed.data_ptr(), ids.data_ptr(), 8, 1000, codes.data_ptr(),
                               8, pos.data_ptr(), 1, trials, torch.cuda.current_stream().cuda_stream)
     assert rc == 0
     torch.cuda.synchronize()
@@ -61,7 +62,7 @@ def test_sampler_distribution():
     assert (freq - p).abs().max().item() < 0.04
     assert torch.equal(ids[:, 1], tok + 1000)
     # top-k = 1 is greedy; top-p small keeps only the mode
-    rc = L.b200_decode_sample(logits.data_ptr(), 512, n, 1.0, 0, 0.3, 99, ids.data_ptr(), 8, 0, codes.data_ptr(), 8,
+    rc = L.b200_decode_sample(logits.data_ptr(), 512, n, 1.0, 0, 0.3, seed.data_ptr(), ids.data_ptr(), 8, 0, codes.data_ptr(), 8,
                               pos.data_ptr(), 1, trials, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     assert (codes[:, 0] == 7).all()
