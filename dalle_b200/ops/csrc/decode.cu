@@ -99,53 +99,109 @@ __global__ void decode_ln_shift_kernel(const float* __restrict__ x, const float*
   }
 }
 
-// one warp per (sample, head); each lane owns 2 of the 64 head dims for the output, keys are processed one by one
-// by the whole warp (dot product = 2 FMAs per lane + warp reduce).  n_keys <= 257 + 32 (+ conv window).
-__global__ void decode_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ kcache,
-                                   __nv_bfloat16* __restrict__ vcache, __nv_bfloat16* __restrict__ out,
-                                   const int* __restrict__ pos_ptr, DecGeom g, int mode) {
-  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+// one warp per (sample, head).  Phase 1: lanes <-> keys (each lane dots q with whole K rows, independent loads);
+// phase 2: warp softmax; phase 3: lanes <-> head dims, streaming the V rows (coalesced 128 B per key).
+constexpr int DEC_MAX_KEYS = 352;   // 257 text + 32 axial (+ window) rounded up
+__global__ void __launch_bounds__(128)
+decode_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ kcache,
+                   __nv_bfloat16* __restrict__ vcache, __nv_bfloat16* __restrict__ out,
+                   const int* __restrict__ pos_ptr, DecGeom g, int mode) {
+  __shared__ float sq[4][64];
+  __shared__ float sp[4][DEC_MAX_KEYS];
+  __shared__ int spos[4][DEC_MAX_KEYS];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * 4 + w;
   if (wid >= g.B * g.H) return;
   const int b = wid / g.H, h = wid - b * g.H, pos = *pos_ptr;
   const int HD = g.H * 64;
   const __nv_bfloat16* row = qkv + static_cast<long long>(b) * 3 * HD + h * 64 + lane * 2;
   const float2 q = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(row));
-  const uint32_t kk = *reinterpret_cast<const uint32_t*>(row + HD);
-  const uint32_t vv = *reinterpret_cast<const uint32_t*>(row + 2 * HD);
   const long long cbase = (static_cast<long long>(b) * g.H + h) * g.seq * 64;
-  *reinterpret_cast<uint32_t*>(kcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) = kk;
-  *reinterpret_cast<uint32_t*>(vcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) = vv;
-  __syncwarp();
+  *reinterpret_cast<uint32_t*>(kcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) =
+      *reinterpret_cast<const uint32_t*>(row + HD);
+  *reinterpret_cast<uint32_t*>(vcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) =
+      *reinterpret_cast<const uint32_t*>(row + 2 * HD);
+  sq[w][lane * 2] = q.x;
+  sq[w][lane * 2 + 1] = q.y;
 
-  float m = -1e30f, l = 0.f, a0 = 0.f, a1 = 0.f;
-  auto visit = [&](int j) {
-    const uint32_t ku = (j == pos) ? kk : *reinterpret_cast<const uint32_t*>(kcache + cbase + static_cast<long long>(j) * 64 + lane * 2);
-    const uint32_t vu = (j == pos) ? vv : *reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(j) * 64 + lane * 2);
-    const float2 kf = unpack_bf16x2(ku), vf = unpack_bf16x2(vu);
-    const float s = warp_sum(q.x * kf.x + q.y * kf.y) * kLog2eDec;
-    const float mn = fmaxf(m, s);
-    const float corr = exp2f(m - mn), p = exp2f(s - mn);
-    l = l * corr + p;
-    a0 = a0 * corr + p * vf.x;
-    a1 = a1 * corr + p * vf.y;
-    m = mn;
-  };
+  // ---- the list of key positions this query may attend to ----
+  int n_keys;
   if (pos < g.T) {
-    for (int j = 0; j <= pos; ++j) visit(j);
+    n_keys = pos + 1;
+    for (int i = lane; i < n_keys; i += 32) spos[w][i] = i;
   } else {
-    for (int j = 0; j < g.T; ++j) visit(j);
+    for (int i = lane; i < g.T; i += 32) spos[w][i] = i;
     const int p = pos - g.T, r = p / g.F, c = p - r * g.F;
     if (mode == 1) {
-      for (int cc = 0; cc <= c; ++cc) visit(g.T + r * g.F + cc);
+      n_keys = g.T + c + 1;
+      for (int i = lane; i <= c; i += 32) spos[w][g.T + i] = g.T + r * g.F + i;
     } else if (mode == 2) {
-      for (int rr = 0; rr <= r; ++rr) visit(g.T + rr * g.F + c);
+      n_keys = g.T + r + 1;
+      for (int i = lane; i <= r; i += 32) spos[w][g.T + i] = g.T + i * g.F + c;
     } else if (mode == 3) {
-      for (int rr = max(0, r - g.conv_half); rr <= r; ++rr)
-        for (int cc = max(0, c - g.conv_half); cc <= min(g.F - 1, c + g.conv_half); ++cc)
-          if (rr * g.F + cc <= p) visit(g.T + rr * g.F + cc);
+      int cnt = 0;
+      if (lane == 0) {
+        for (int rr = max(0, r - g.conv_half); rr <= r; ++rr)
+          for (int cc = max(0, c - g.conv_half); cc <= min(g.F - 1, c + g.conv_half); ++cc)
+            if (rr * g.F + cc <= p) spos[w][g.T + cnt++] = g.T + rr * g.F + cc;
+      }
+      n_keys = g.T + __shfl_sync(0xffffffffu, cnt, 0);
     } else {
-      for (int j = g.T; j <= pos; ++j) visit(j);
+      n_keys = min(pos + 1, DEC_MAX_KEYS);
+      for (int i = g.T + lane; i < n_keys; i += 32) spos[w][i] = i;
     }
+  }
+  __syncwarp();
+
+  // ---- phase 1: scores ----
+  float mx = -1e30f;
+  for (int i = lane; i < n_keys; i += 32) {
+    const uint4* kr = reinterpret_cast<const uint4*>(kcache + cbase + static_cast<long long>(spos[w][i]) * 64);
+    float s = 0.f;
+#pragma unroll
+    for (int c8 = 0; c8 < 8; ++c8) {
+      const uint4 u = kr[c8];
+      float2 f;
+      const float* qq = &sq[w][c8 * 8];
+      f = unpack_bf16x2(u.x); s += f.x * qq[0] + f.y * qq[1];
+      f = unpack_bf16x2(u.y); s += f.x * qq[2] + f.y * qq[3];
+      f = unpack_bf16x2(u.z); s += f.x * qq[4] + f.y * qq[5];
+      f = unpack_bf16x2(u.w); s += f.x * qq[6] + f.y * qq[7];
+    }
+    s *= kLog2eDec;
+    sp[w][i] = s;
+    mx = fmaxf(mx, s);
+  }
+  mx = warp_max(mx);
+  // ---- phase 2: probabilities ----
+  float l = 0.f;
+  for (int i = lane; i < n_keys; i += 32) {
+    const float p = exp2f(sp[w][i] - mx);
+    sp[w][i] = p;
+    l += p;
+  }
+  l = warp_sum(l);
+  __syncwarp();
+  // ---- phase 3: weighted sum of V rows; lane owns dims (2*lane, 2*lane+1) ----
+  float a0 = 0.f, a1 = 0.f;
+  int i = 0;
+  for (; i + 4 <= n_keys; i += 4) {
+    uint32_t vu[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      vu[j] = *reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[w][i + j]) * 64 + lane * 2);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 vf = unpack_bf16x2(vu[j]);
+      const float p = sp[w][i + j];
+      a0 += p * vf.x;
+      a1 += p * vf.y;
+    }
+  }
+  for (; i < n_keys; ++i) {
+    const float2 vf = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[w][i]) * 64 + lane * 2));
+    a0 += sp[w][i] * vf.x;
+    a1 += sp[w][i] * vf.y;
   }
   const float inv = 1.0f / l;
   *reinterpret_cast<uint32_t*>(out + static_cast<long long>(b) * HD + h * 64 + lane * 2) = pack_bf16x2(a0 * inv, a1 * inv);
@@ -275,7 +331,8 @@ extern "C" int b200_decode_ln_shift(const float* x, const float* x2, const float
 extern "C" int b200_decode_attn(const void* qkv, void* kcache, void* vcache, void* out, const int* pos_ptr, int B,
                                 int H, int seq, int T, int F, int mode, int conv_kernel, void* stream) {
   DecGeom g{B, H * 64, H, seq, T, F, conv_kernel / 2};
-  decode_attn_kernel<<<(B * H * 32 + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  if (T + F + 32 > DEC_MAX_KEYS && mode != 0) return -74;
+  decode_attn_kernel<<<(B * H + 3) / 4, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(kcache),
       reinterpret_cast<__nv_bfloat16*>(vcache), reinterpret_cast<__nv_bfloat16*>(out), pos_ptr, g, mode);
   return derr();
