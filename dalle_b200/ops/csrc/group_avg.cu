@@ -47,6 +47,7 @@ struct GroupArgs {
   uint32_t epoch;                     // barrier values epoch+1 .. epoch+4 are used by this launch
   int payload_mode;                   // 0 = fp32 P2P loads, 1 = bf16 payload
   int zero_grad;
+  int reduce_only;                    // 1: stop after the reduce phase and give EVERY rank the reduced gradient
   // local optimizer state (shard only is touched)
   uint8_t* q1; uint8_t* q2; float* f1; float* f2; float* absmax1; float* absmax2;
   const float* code1; const float* code2;
@@ -143,8 +144,19 @@ group_lamb_kernel(const GroupArgs a) {
                                    acc[j + 2] * a.hp.grad_scale, acc[j + 3] * a.hp.grad_scale);
       ssq += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
       bad |= !(isfinite(v.x) && isfinite(v.y) && isfinite(v.z) && isfinite(v.w));
-      *reinterpret_cast<float4*>(g_local + base + j) = v;
+      if (a.reduce_only) {
+        for (int r = 0; r < a.world; ++r)
+          *reinterpret_cast<float4*>(a.grad[(a.rank + r) % a.world] + base + j) = v;  // all-gather of the mean gradient
+      } else {
+        *reinterpret_cast<float4*>(g_local + base + j) = v;
+      }
     }
+  }
+  if (a.reduce_only) {
+    rank_barrier(a, a.epoch + 2, grid);
+    rank_barrier(a, a.epoch + 3, grid);
+    rank_barrier(a, a.epoch + 4, grid);  // keep the epoch arithmetic identical to a full step
+    return;
   }
   ssq = block_sum(ssq, sred);
   if (threadIdx.x == 0) atomicAdd(&a.stats[0], ssq);
@@ -333,6 +345,7 @@ extern "C" int b200_group_lamb_step(const B200Group* d, void* stream) {
   }
   a.xstride = d->xstride; a.n_tensors = d->n_tensors; a.n_blocks = d->n_blocks;
   a.blk0 = d->blk0; a.blk1 = d->blk1; a.epoch = d->epoch; a.payload_mode = d->payload_mode; a.zero_grad = d->zero_grad;
+  a.reduce_only = d->reduce_only;
   a.q1 = reinterpret_cast<uint8_t*>(d->q1); a.q2 = reinterpret_cast<uint8_t*>(d->q2);
   a.f1 = d->f1; a.f2 = d->f2; a.absmax1 = d->absmax1; a.absmax2 = d->absmax2;
   a.code1 = d->code1; a.code2 = d->code2;

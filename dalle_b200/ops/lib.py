@@ -41,7 +41,7 @@ class B200Group(ctypes.Structure):
         ("payload_ptrs", ctypes.c_void_p * 8), ("signal_ptrs", ctypes.c_void_p * 8), ("xchg_ptrs", ctypes.c_void_p * 8),
         ("xstride", ctypes.c_int), ("n_tensors", ctypes.c_int), ("n_blocks", ctypes.c_int),
         ("blk0", ctypes.c_int), ("blk1", ctypes.c_int), ("epoch", ctypes.c_uint), ("payload_mode", ctypes.c_int),
-        ("zero_grad", ctypes.c_int),
+        ("zero_grad", ctypes.c_int), ("reduce_only", ctypes.c_int),
         ("q1", ctypes.c_void_p), ("q2", ctypes.c_void_p), ("f1", ctypes.c_void_p), ("f2", ctypes.c_void_p),
         ("absmax1", ctypes.c_void_p), ("absmax2", ctypes.c_void_p), ("code1", ctypes.c_void_p),
         ("code2", ctypes.c_void_p), ("blocks", ctypes.c_void_p), ("wd_per_tensor", ctypes.c_void_p),

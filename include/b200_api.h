@@ -134,6 +134,7 @@ typedef struct B200Group {
   unsigned int epoch;
   int payload_mode;   /* 0: fp32 gradients read over NVLink; 1: bf16 payload (half the bytes) */
   int zero_grad;
+  int reduce_only;    /* 1: only reduce; every rank ends with grad_scale * sum of all ranks' gradients */
   void* q1; void* q2; float* f1; float* f2; float* absmax1; float* absmax2;
   const float* code1; const float* code2; const void* blocks; const float* wd_per_tensor;
   float* tensor_sums; float* stats /* [4] */; float* trust_out;
