@@ -9,6 +9,7 @@ joins the TCP swarm (DHT progress, matchmaking, compressed butterfly all-reduce)
 Covers BASELINE config 5 and the "one host feeds N accelerator workers" capability of the reference's
 run_trainer_tpu.py."""
 import logging
+import os
 import time
 
 import torch
@@ -50,9 +51,10 @@ def main(argv=None):
                                       matchmaking_time=collab_args.matchmaking_time,
                                       averaging_timeout=collab_args.averaging_timeout,
                                       allreduce_timeout=collab_args.allreduce_timeout, grad_compression=comp,
+                                      target_group_size=int(os.environ.get("DALLE_B200_TARGET_GROUP_SIZE", "0")) or None,
                                       tracker_opts=dict(min_refresh_period=0.5, default_refresh_period=1.0,
                                                         max_refresh_period=3.0))
-    gen = torch.Generator().manual_seed(1000 * a.seed + 17 * rank + hash(peer_args.experiment_prefix) % 1000)
+    gen = torch.Generator().manual_seed(1000 * a.seed + 17 * rank + int(os.environ.get("DALLE_B200_DATA_SEED", "0")))
     B = a.per_device_train_batch_size
     loss_sum, steps, reported = 0.0, 0, -1
     for it in range(int(min(a.max_steps, 10 ** 9))):

@@ -9,7 +9,7 @@ work = os.path.join(ROOT, "gpurun_out", "config5")
 os.makedirs(work, exist_ok=True)
 env = dict(os.environ, PYTHONPATH=ROOT, PYTHONUNBUFFERED="1")
 common = ["--experiment_prefix", "cfg5", "--authorize", "false", "--model_preset", preset, "--target_batch_size", "64",
-          "--matchmaking_time", "3", "--averaging_timeout", "60", "--allreduce_timeout", "30"]
+          "--matchmaking_time", "20", "--averaging_timeout", "60", "--allreduce_timeout", "30"]
 aux_log = os.path.join(work, "aux.log")
 aux = subprocess.Popen([sys.executable, os.path.join(ROOT, "run_aux_peer.py"), *common, "--no_cuda", "true",
                         "--host_maddrs", "/ip4/127.0.0.1/tcp/0", "--refresh_period", "1", "--store_checkpoints", "false",
@@ -30,7 +30,7 @@ for gi in range(2):
            "--host_maddrs", "/ip4/127.0.0.1/tcp/0", "--per_device_train_batch_size", "4", "--max_steps", "24",
            "--seed", "0", "--learning_rate", "0.01", "--warmup_steps", "1"]
     groups.append(subprocess.Popen(cmd, stdout=open(os.path.join(work, f"group{gi}.log"), "w"), stderr=subprocess.STDOUT,
-                                   env=dict(env, CUDA_VISIBLE_DEVICES=devs), cwd=work))
+                                   env=dict(env, CUDA_VISIBLE_DEVICES=devs, DALLE_B200_TARGET_GROUP_SIZE="2", DALLE_B200_DATA_SEED=str(gi + 1)), cwd=work))
 rcs = [g.wait(timeout=500) for g in groups]
 time.sleep(3)
 aux.terminate()
