@@ -42,10 +42,12 @@ print("swarm-averaged rounds:", [l.count("swarm-averaged") for l in logs], "grou
 print("aux epochs:", re.findall(r"Epoch #(\d+)", auxl)[-5:])
 ok = all(r == 0 for r in rcs) and all(done) and all(int(d.group(1)) >= 2 for d in done) and \
     all(l.count("swarm-averaged") >= 1 for l in logs) and re.search(r"Epoch #\d+", auxl)
-if ok and done[0].group(2) == done[1].group(2):
-    print("CONFIG5_OK (both groups hold identical parameters)")
-elif ok:
-    print("CONFIG5_OK_BUT_PARAMS_DIFFER", done[0].group(2), done[1].group(2))
+if ok:
+    a, b = float(done[0].group(2)), float(done[1].group(2))
+    # gradients travel 8-bit compressed and every peer applies x += delta (hivemind semantics), so the two groups
+    # agree up to the compression error, not bit for bit
+    rel = abs(a - b) / max(abs(a), 1e-9)
+    print(f"CONFIG5_OK param checksums {a} vs {b} (rel diff {rel:.2e})" if rel < 1e-4 else f"CONFIG5_DRIFT {a} {b}")
 else:
     print("CONFIG5_FAIL")
     for l in logs: print(l[-2500:])
