@@ -56,7 +56,7 @@ def _run(cmd):
 
 def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     srcs = sorted(CSRC.glob("*.cu"))
-    deps = srcs + sorted(CSRC.glob("*.cuh")) + sorted((ROOT / "include").glob("*.h"))
+    deps = srcs + sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.inc")) + sorted((ROOT / "include").glob("*.h"))
     stamp = BUILD_DIR / "cuda.stamp"
     dig = _digest(deps, NVCC_FLAGS)
     if not force and CUDA_LIB.exists() and stamp.exists() and stamp.read_text() == dig:
@@ -69,7 +69,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
         obj = BUILD_DIR / (src.stem + ".o")
         # per-file incremental: skip when neither the file nor any header changed
         fstamp = BUILD_DIR / (src.stem + ".stamp")
-        fdig = _digest([src] + sorted(CSRC.glob("*.cuh")) + sorted((ROOT / "include").glob("*.h")), NVCC_FLAGS)
+        fdig = _digest([src] + sorted(CSRC.glob("*.cuh")) + sorted(CSRC.glob("*.inc")) + sorted((ROOT / "include").glob("*.h")), NVCC_FLAGS)
         if not force and obj.exists() and fstamp.exists() and fstamp.read_text() == fdig:
             return obj
         extra = ["-Xptxas", "-v"] if verbose else []

@@ -330,7 +330,7 @@ int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t1
 
 using namespace b200;
 
-extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
+extern "C" int b200_attn_fwd_v1(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
                              int conv_kernel, void* stream) {
   AttnGeom g;
   g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
