@@ -44,4 +44,11 @@ __device__ __forceinline__ uint32_t sw128_offset(int row, int chunk16) {
 
 constexpr float kLog2e = 1.4426950408889634f;
 
+// single MUFU.EX2 (exp2f() adds range handling that the softmax does not need)
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 }  // namespace b200

@@ -12,12 +12,15 @@
 #include "attn_common.cuh"
 #include "b200_api.h"
 
+#include <cstdio>
+#include <cstdlib>
+
 namespace b200 {
 
 int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
                    CUtensorMap* taux);
 
-constexpr int AF2_THREADS = 192;
+constexpr int AF2_THREADS = 128;
 constexpr int AF2_MAXK = 144;                       // keys per chunk
 constexpr int AF2_KV_BYTES = AF2_MAXK * 128;        // 18 KiB
 constexpr int AF2_P_BYTES = 3 * 16384;              // three 64-key K-major tiles
@@ -87,8 +90,6 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constan
   uint64_t* bar_s = bars + 3;
   uint64_t* bar_p = bars + 4;
   uint64_t* bar_o = bars + 5;
-  uint64_t* k_empty = bars + 6;
-  uint64_t* v_empty = bars + 7;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -96,15 +97,15 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constan
   const int q0 = blk * 128;
   const int n_chunks = af2_num_chunks<MODE>(g, blk);
 
-  if (warp == 0 && lane == 0) {
+  if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm128);
     tma_prefetch_desc(&tmTail);
     tma_prefetch_desc(&tmAux);
     mbar_init(bar_q, 1); mbar_init(bar_k, 1); mbar_init(bar_v, 1); mbar_init(bar_s, 1);
-    mbar_init(bar_p, 128); mbar_init(bar_o, 1); mbar_init(k_empty, 1); mbar_init(v_empty, 1);
+    mbar_init(bar_p, 128); mbar_init(bar_o, 1);
     fence_barrier_init();
   }
-  if (warp == 1) {
+  if (warp == 0) {
     tmem_alloc(tmem_slot, 256);
     tmem_relinquish();
   }
@@ -113,76 +114,72 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constan
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 0) {
-    if (lane == 0) {
-      const int row_base = b * g.seq;
-      const int lines = 128 / g.F;
-      mbar_expect_tx(bar_q, 16384);
-      if (MODE == ATT_COL) {
-        for (int l = 0; l < lines; ++l) tma_load_4d(sQ + l * g.F * 128, &tmAux, bar_q, h * 64, blk * lines + l, 0, b);
-      } else {
-        tma_load_2d(sQ, &tm128, bar_q, h * 64, row_base + ((MODE == ATT_TEXT) ? q0 : g.T + q0));
-      }
-      for (int c = 0; c < n_chunks; ++c) {
-        const ChunkDesc d = af2_chunk<MODE>(g, c);
-        const uint32_t bytes = static_cast<uint32_t>(d.n_text + d.n_local) * 128u;
-        for (int sect = 0; sect < 2; ++sect) {
-          uint64_t* full = sect == 0 ? bar_k : bar_v;
-          uint64_t* empty = sect == 0 ? k_empty : v_empty;
-          uint8_t* dst = sect == 0 ? sK : sV;
-          const int col = (sect == 0 ? g.H * 64 : 2 * g.H * 64) + h * 64;
-          mbar_wait(empty, (c & 1) ^ 1);
-          mbar_expect_tx(full, bytes);
-          if (d.n_text == 128) tma_load_2d(dst, &tm128, full, col, row_base + d.key0);
-          else if (d.n_text > 0) tma_load_2d(dst, &tmTail, full, col, row_base + d.key0);
-          uint8_t* dl = dst + d.n_text * 128;
-          if (d.n_local > 0) {
-            if (MODE == ATT_ROW) {
-              tma_load_2d(dl, &tm128, full, col, row_base + g.T + q0);
-            } else if (MODE == ATT_COL) {
-              for (int l = 0; l < lines; ++l) tma_load_4d(dl + l * g.F * 128, &tmAux, full, col, blk * lines + l, 0, b);
-            } else if (MODE == ATT_CONV) {
-              if (d.j0 == 0) tma_load_2d(dl, &tm128, full, col, row_base + g.T + q0 - 2 * g.F);
-              else tma_load_2d(dl, &tmAux, full, col, row_base + g.T + q0 - 2 * g.F + 128);  // box rows = 2F
-            }
-          }
-        }
+  // Thread 0 is also the TMA producer and the MMA issuer (single-thread instructions); a 128-thread CTA keeps the
+  // register allocation at 4 warps so that two CTAs share an SM.
+  const int row_base = b * g.seq;
+  const int lines = 128 / g.F;
+  auto load_kv = [&](int c, int sect) {
+    const ChunkDesc d = af2_chunk<MODE>(g, c);
+    uint64_t* full = sect == 0 ? bar_k : bar_v;
+    uint8_t* dst = sect == 0 ? sK : sV;
+    const int col = (sect == 0 ? g.H * 64 : 2 * g.H * 64) + h * 64;
+    mbar_expect_tx(full, static_cast<uint32_t>(d.n_text + d.n_local) * 128u);
+    if (d.n_text == 128) tma_load_2d(dst, &tm128, full, col, row_base + d.key0);
+    else if (d.n_text > 0) tma_load_2d(dst, &tmTail, full, col, row_base + d.key0);
+    uint8_t* dl = dst + d.n_text * 128;
+    if (d.n_local > 0) {
+      if (MODE == ATT_ROW) {
+        tma_load_2d(dl, &tm128, full, col, row_base + g.T + q0);
+      } else if (MODE == ATT_COL) {
+        for (int l = 0; l < lines; ++l) tma_load_4d(dl + l * g.F * 128, &tmAux, full, col, blk * lines + l, 0, b);
+      } else if (MODE == ATT_CONV) {
+        if (d.j0 == 0) tma_load_2d(dl, &tm128, full, col, row_base + g.T + q0 - 2 * g.F);
+        else tma_load_2d(dl, &tmAux, full, col, row_base + g.T + q0 - 2 * g.F + 128);  // box rows = 2F
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      mbar_wait(bar_q, 0);
-      const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV), p_addr = smem_u32(sP);
-      const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);
-      for (int c = 0; c < n_chunks; ++c) {
-        const ChunkDesc d = af2_chunk<MODE>(g, c);
-        const int n = d.n_text + d.n_local;
-        mbar_wait(bar_k, c & 1);
-        tc_fence_after();
-        const uint32_t idesc_s = make_idesc_bf16(128, n, 0, 0);
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          umma_bf16_ss(tmem + AF2_TM_S, make_smem_desc_sw128(q_addr + kk * 32, 0, 1024),
-                       make_smem_desc_sw128(k_addr + kk * 32, 0, 1024), idesc_s, kk > 0 ? 1u : 0u);
-        umma_commit(bar_s);
-        umma_commit(k_empty);
-        mbar_wait(bar_p, c & 1);
-        mbar_wait(bar_v, c & 1);
-        tc_fence_after();
-        for (int k16 = 0; k16 < n / 16; ++k16)
-          umma_bf16_ss(tmem + AF2_TM_O, make_smem_desc_sw128(p_addr + (k16 >> 2) * 16384 + (k16 & 3) * 32, 0, 1024),
-                       make_smem_desc_sw128(v_addr + k16 * 2048, 8192, 1024), idesc_pv, k16 > 0 ? 1u : 0u);
-        umma_commit(bar_o);
-        umma_commit(v_empty);
-      }
+  };
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar_q, 16384);
+    if (MODE == ATT_COL) {
+      for (int l = 0; l < lines; ++l) tma_load_4d(sQ + l * g.F * 128, &tmAux, bar_q, h * 64, blk * lines + l, 0, b);
+    } else {
+      tma_load_2d(sQ, &tm128, bar_q, h * 64, row_base + ((MODE == ATT_TEXT) ? q0 : g.T + q0));
     }
-  } else {
-#include "attn_fwd2_softmax.inc"
+    load_kv(0, 0);
+    load_kv(0, 1);
   }
+  const uint32_t q_addr = smem_u32(sQ), k_addr = smem_u32(sK), v_addr = smem_u32(sV), p_addr = smem_u32(sP);
+  auto issue_s = [&](int c) {       // thread 0
+    const ChunkDesc d = af2_chunk<MODE>(g, c);
+    if (c == 0) mbar_wait(bar_q, 0);
+    mbar_wait(bar_k, c & 1);
+    tc_fence_after();
+    const uint32_t idesc_s = make_idesc_bf16(128, d.n_text + d.n_local, 0, 0);
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk)
+      umma_bf16_ss(tmem + AF2_TM_S, make_smem_desc_sw128(q_addr + kk * 32, 0, 1024),
+                   make_smem_desc_sw128(k_addr + kk * 32, 0, 1024), idesc_s, kk > 0 ? 1u : 0u);
+    umma_commit(bar_s);
+  };
+  auto issue_pv = [&](int c) {      // thread 0, after every softmax thread arrived on bar_p
+    const ChunkDesc d = af2_chunk<MODE>(g, c);
+    mbar_wait(bar_p, c & 1);
+    mbar_wait(bar_v, c & 1);
+    tc_fence_after();
+    const uint32_t idesc_pv = make_idesc_bf16(128, 64, 0, 1);
+    for (int k16 = 0; k16 < (d.n_text + d.n_local) / 16; ++k16)
+      umma_bf16_ss(tmem + AF2_TM_O, make_smem_desc_sw128(p_addr + (k16 >> 2) * 16384 + (k16 & 3) * 32, 0, 1024),
+                   make_smem_desc_sw128(v_addr + k16 * 2048, 8192, 1024), idesc_pv, k16 > 0 ? 1u : 0u);
+    umma_commit(bar_o);
+  };
+  if (threadIdx.x == 0) issue_s(0);
+  __syncwarp();
+
+#include "attn_fwd2_softmax.inc"
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == 0) {
     tc_fence_after();
     tmem_dealloc(tmem, 256);
   }
@@ -194,6 +191,7 @@ static int launch_fwd2(const CUtensorMap& t128, const CUtensorMap& ttail, const 
   auto kern = attn_fwd2_kernel<MODE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, AF2_SMEM);
   if (e != cudaSuccess) return -21;
+  cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   dim3 grid(nblocks, a.g.H, a.g.B);
   kern<<<grid, AF2_THREADS, AF2_SMEM, st>>>(t128, ttail, taux, a);
   return cudaGetLastError() == cudaSuccess ? 0 : -22;
@@ -203,12 +201,18 @@ static int launch_fwd2(const CUtensorMap& t128, const CUtensorMap& ttail, const 
 
 using namespace b200;
 
+extern "C" int b200_attn_fwd_v1(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
+                                int conv_kernel, void* stream);
+
 extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
                              int conv_kernel, void* stream) {
   AttnGeom g;
   g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
   g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = conv_kernel / 2;
   if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
+  // the softmax warps assume that a query's local keys sit inside its own 32-key window (grid side 16 or 32);
+  // wider grids take the first-generation kernel, which keeps whole score rows in TMEM
+  if (32 % F) return b200_attn_fwd_v1(qkv, out, lse, B, H, seq, T, F, mode, conv_kernel, stream);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   AttnFwd2Args a;
   a.g = g; a.out = reinterpret_cast<__nv_bfloat16*>(out); a.lse = lse; a.ld_out = H * 64;
