@@ -23,7 +23,7 @@ int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t*
 int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
                    CUtensorMap* taux);
 
-constexpr int ATTB_THREADS = 192;
+constexpr int ATTB_THREADS = 320;   // TMA warp, MMA warp, 8 worker warps
 
 struct AttnBwdArgs {
   AttnGeom g;
@@ -103,7 +103,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     mbar_init(bar_q, 1);
     for (int s = 0; s < 2; ++s) { mbar_init(&kv_full[s], 1); mbar_init(&kv_empty[s], 1); }
     mbar_init(bar_s, 1);
-    mbar_init(bar_pds, 128);
+    mbar_init(bar_pds, 256);
     mbar_init(bar_mma2, 1);
     fence_barrier_init();
   }
@@ -136,7 +136,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       for (int c = 0; c < n_chunks; ++c) {
         const int s = c & 1;
         const uint32_t ph = (c >> 1) & 1;
-        mbar_wait(&kv_empty[s], ph ^ 1);
+        mbar_wait_backoff(&kv_empty[s], ph ^ 1, 64);
         mbar_expect_tx(&kv_full[s], 32768);
         uint8_t* dk = sK + s * 16384;
         uint8_t* dv = sV + s * 16384;
@@ -163,7 +163,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     if (lane == 0) {
       mbar_wait(bar_q, 0);
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO), p_addr = smem_u32(sP), ds_addr = smem_u32(sDS);
-      constexpr uint32_t id_s = make_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t id_dq = make_idesc_bf16(128, 64, 0, 1);
       constexpr uint32_t id_dkv = make_idesc_bf16(128, 64, 1, 1);
       for (int c = 0; c < n_chunks; ++c) {
@@ -172,19 +171,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         mbar_wait(&kv_full[s], ph);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(sK + s * 16384), v_addr = smem_u32(sV + s * 16384);
+        // a short text tail (T mod 128 keys, padded to 16) only needs that many score columns / dQ k-steps
+        const int nkeys = (c < n_text_chunks) ? min(128, g.T_pad - c * 128) : 128;
+        const uint32_t id_sn = make_idesc_bf16(128, nkeys, 0, 0);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
           umma_bf16_ss(tmem + TM_S, make_smem_desc_sw128(q_addr + kk * 32, 0, 1024),
-                       make_smem_desc_sw128(k_addr + kk * 32, 0, 1024), id_s, kk > 0);
+                       make_smem_desc_sw128(k_addr + kk * 32, 0, 1024), id_sn, kk > 0);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
           umma_bf16_ss(tmem + TM_DP, make_smem_desc_sw128(do_addr + kk * 32, 0, 1024),
-                       make_smem_desc_sw128(v_addr + kk * 32, 0, 1024), id_s, kk > 0);
+                       make_smem_desc_sw128(v_addr + kk * 32, 0, 1024), id_sn, kk > 0);
         umma_commit(bar_s);
-        mbar_wait(bar_pds, c & 1);
+        mbar_wait_backoff(bar_pds, c & 1);
         tc_fence_after();
-#pragma unroll
-        for (int k16 = 0; k16 < 8; ++k16) {
+        for (int k16 = 0; k16 < nkeys / 16; ++k16) {
           // dQ += dS K   (A = dS K-major over keys; B = K read MN-major: N = 64 dims, K = keys)
           umma_bf16_ss(tmem + TM_DQ, make_smem_desc_sw128(ds_addr + (k16 >> 2) * 16384 + (k16 & 3) * 32, 0, 1024),
                        make_smem_desc_sw128(k_addr + k16 * 2048, 8192, 1024), id_dq, (c > 0 || k16 > 0));
@@ -204,7 +205,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       }
     }
   } else {
+    // ---- 8 worker warps: warps w and w+4 share TMEM lane quarter (w & 3) and split the column work ----
     const int qw = warp & 3;
+    const int part = (warp - 2) >> 2;   // 0: column groups 0,1 / dK / dQ dims 0-31   1: groups 2,3 / dV / dims 32-63
     const int i = qw * 32 + lane;
     const uint32_t trow = tmem + (static_cast<uint32_t>(qw * 32) << 16);
     int tpos, ip = 0, ir = 0, ic = 0;
@@ -223,51 +226,68 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     const float lse_i = q_valid ? a.lse[bh * g.seq + tpos] : 0.f;
     const float delta_i = q_valid ? a.delta[bh * g.seq + tpos] : 0.f;
     const int win0 = qw * 32;
+    // validity bits of the local keys this row can see, relative to win0 (same construction as the forward)
+    uint32_t lmask[3] = {0u, 0u, 0u};
+    if (MODE == ATT_ROW || MODE == ATT_COL) {
+      const int lo = max(i - (MODE == ATT_ROW ? ic : ir), win0) - win0;
+      lmask[0] = (0xFFFFFFFFu >> (31 - lane)) & (0xFFFFFFFFu << lo);
+    }
+    if (MODE == ATT_CONV) {
+      for (int dr = 0; dr <= g.conv_half; ++dr)
+        for (int dc = -g.conv_half; dc <= g.conv_half; ++dc) {
+          const int kr = ir - dr, kc = ic + dc;
+          const int kp = kr * g.F + kc;
+          const int j = kp - (q0 - 2 * g.F) - win0;
+          if (kr >= 0 && kc >= 0 && kc < g.F && kp <= ip && j >= 0 && j < 96) lmask[j >> 5] |= 1u << (j & 31);
+        }
+    }
+    const int text_limit = (MODE == ATT_TEXT) ? min(tpos + 1, g.T) : g.T;
+    uint8_t* pbase = sP + part * 16384 + i * 128;   // this warp's column groups live in 64-key tile `part`
+    uint8_t* dsbase = sDS + part * 16384 + i * 128;
+    const int sw = i & 7;
 
     for (int c = 0; c < n_chunks; ++c) {
       const bool is_text = c < n_text_chunks;
       const int lc = c - n_text_chunks;
+      const int nkeys = is_text ? min(128, g.T_pad - c * 128) : 128;   // keys the chunk's MMAs cover
       mbar_wait(bar_s, c & 1);
       tc_fence_after();
       // ---- P and dS for this chunk ----
-#pragma unroll 1
-      for (int cc = 0; cc < 4; ++cc) {
-        const int j0 = cc * 32;
-        bool any = q_valid;
-        if (any && !is_text) {
-          if (MODE == ATT_ROW || MODE == ATT_COL) any = (j0 == win0);
-          if (MODE == ATT_CONV) {
-            const int jg0 = lc * 128 + j0;  // global local-key index of this 32-column group
-            any = (jg0 + 32 > win0) && (jg0 < win0 + 32 + 2 * g.F);
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        const int j0 = (part * 2 + t) * 32;
+        if (j0 >= nkeys) continue;   // beyond a short text tail: columns are not read by the dQ MMA
+        uint32_t vm = 0u;
+        if (q_valid) {
+          if (is_text) {
+            const int nv = text_limit - (c * 128 + j0);
+            vm = nv <= 0 ? 0u : (nv >= 32 ? 0xFFFFFFFFu : (1u << nv) - 1u);
+          } else if (MODE == ATT_ROW || MODE == ATT_COL) {
+            vm = (j0 == win0) ? lmask[0] : 0u;
+          } else if (MODE == ATT_CONV) {
+            const int jrel = lc * 128 + j0 - win0;
+            vm = (jrel >= 0 && jrel < 96) ? lmask[jrel >> 5] : 0u;
           }
         }
         float p[32], ds[32];
-        if (__any_sync(0xffffffffu, any)) {
+        if (__any_sync(0xffffffffu, vm != 0u)) {
           uint32_t rs[32], rp[32];
           tmem_ld32(trow + TM_S + j0, rs);
           tmem_ld32(trow + TM_DP + j0, rp);
           tmem_ld_wait();
+          if (__all_sync(0xffffffffu, vm == 0xFFFFFFFFu)) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            bool valid;
-            const int jj = j0 + j;
-            if (is_text) {
-              const int kt = c * 128 + jj;
-              valid = (MODE == ATT_TEXT) ? (kt <= tpos) : (kt < g.T);
-            } else if (MODE == ATT_ROW || MODE == ATT_COL) {
-              valid = (jj / g.F == i / g.F) && (jj <= i);
-            } else {
-              const int kp = q0 - 2 * g.F + lc * 128 + jj;
-              valid = false;
-              if (kp >= 0 && kp <= ip) {
-                const int kr = kp / g.F, kc = kp - kr * g.F;
-                valid = (ir - kr <= g.conv_half) && (ic - kc <= g.conv_half) && (kc - ic <= g.conv_half);
-              }
+            for (int j = 0; j < 32; ++j) {
+              p[j] = fast_exp2(__uint_as_float(rs[j]) * kLog2e - lse_i);
+              ds[j] = p[j] * (__uint_as_float(rp[j]) - delta_i);
             }
-            valid = valid && any;
-            const float pe = exp2f(__uint_as_float(rs[j]) * kLog2e - lse_i);
-            p[j] = valid ? pe : 0.f;
-            ds[j] = valid ? pe * (__uint_as_float(rp[j]) - delta_i) : 0.f;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float pe = ((vm >> j) & 1u) ? fast_exp2(__uint_as_float(rs[j]) * kLog2e - lse_i) : 0.f;
+              p[j] = pe;
+              ds[j] = pe * (__uint_as_float(rp[j]) - delta_i);
+            }
           }
         } else {
 #pragma unroll
@@ -275,26 +295,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         }
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
-          const int key0 = j0 + gq * 8;
-          const uint32_t off = (key0 >> 6) * 16384 + sw128_offset(i, (key0 & 63) >> 3);
+          const uint32_t off = static_cast<uint32_t>(((t * 4 + gq) ^ sw) << 4);
           uint4 u;
           u.x = pack_bf16x2(p[gq * 8 + 0], p[gq * 8 + 1]);
           u.y = pack_bf16x2(p[gq * 8 + 2], p[gq * 8 + 3]);
           u.z = pack_bf16x2(p[gq * 8 + 4], p[gq * 8 + 5]);
           u.w = pack_bf16x2(p[gq * 8 + 6], p[gq * 8 + 7]);
-          *reinterpret_cast<uint4*>(sP + off) = u;
+          *reinterpret_cast<uint4*>(pbase + off) = u;
           u.x = pack_bf16x2(ds[gq * 8 + 0], ds[gq * 8 + 1]);
           u.y = pack_bf16x2(ds[gq * 8 + 2], ds[gq * 8 + 3]);
           u.z = pack_bf16x2(ds[gq * 8 + 4], ds[gq * 8 + 5]);
           u.w = pack_bf16x2(ds[gq * 8 + 6], ds[gq * 8 + 7]);
-          *reinterpret_cast<uint4*>(sDS + off) = u;
+          *reinterpret_cast<uint4*>(dsbase + off) = u;
         }
       }
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(bar_pds);
 
-      // ---- dK / dV of this chunk (thread = key row i of the chunk) ----
+      // ---- dK (part 0) / dV (part 1) of this chunk: thread = key row i of the chunk ----
       mbar_wait(bar_mma2, c & 1);
       tc_fence_after();
       int ktok;  // token index of key row i, -1 if it must not be written
@@ -309,43 +328,45 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
         const int kp = q0 - 2 * g.F + lc * 128 + i;
         ktok = (kp >= 0 && kp < g.P - 1 && kp < q0 + 128) ? g.T + kp : -1;
       }
+      if (__any_sync(0xffffffffu, ktok >= 0)) {
+        const bool is_v = part == 1;
 #pragma unroll 1
-      for (int half = 0; half < 4; ++half) {  // 0,1: dK dims 0-31 / 32-63 ; 2,3: dV
-        const bool is_v = half >= 2;
-        const int d0 = (half & 1) * 32;
-        uint32_t r[32];
-        tmem_ld32(trow + (is_v ? TM_DV : TM_DK) + d0, r);
-        tmem_ld_wait();
-        if (ktok < 0) continue;
-        float v[32];
+        for (int half = 0; half < 2; ++half) {
+          const int d0 = half * 32;
+          uint32_t r[32];
+          tmem_ld32(trow + (is_v ? TM_DV : TM_DK) + d0, r);
+          tmem_ld_wait();
+          if (ktok < 0) continue;
+          float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        const long long grow = static_cast<long long>(b) * g.seq + ktok;
-        if (direct) {
-          inv_rotary32(v, a.rot_t + ktok, a.rot_len, d0, 1.0f);
-          store32_bf16(a.dqkv + grow * (3 * HD) + (is_v ? 2 : 1) * HD + h * 64 + d0, v);
-        } else {
-          float* dst = a.kv_acc + grow * (2 * HD) + (is_v ? HD : 0) + h * 64 + d0;
-          if (a.debug_skip_atomics) continue;
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          const long long grow = static_cast<long long>(b) * g.seq + ktok;
+          if (direct) {
+            inv_rotary32(v, a.rot_t + ktok, a.rot_len, d0, 1.0f);
+            store32_bf16(a.dqkv + grow * (3 * HD) + (is_v ? 2 : 1) * HD + h * 64 + d0, v);
+          } else {
+            float* dst = a.kv_acc + grow * (2 * HD) + (is_v ? HD : 0) + h * 64 + d0;
+            if (a.debug_skip_atomics) continue;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+            for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+          }
         }
       }
       tc_fence_before();
     }
 
-    // ---- dQ ----
-#pragma unroll 1
-    for (int half = 0; half < 2; ++half) {
+    // ---- dQ (each part one half of the head dims) ----
+    {
       uint32_t r[32];
-      tmem_ld32(trow + TM_DQ + half * 32, r);
+      tmem_ld32(trow + TM_DQ + part * 32, r);
       tmem_ld_wait();
-      if (!q_valid) continue;
-      float v[32];
+      if (q_valid) {
+        float v[32];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      inv_rotary32(v, a.rot_t + tpos, a.rot_len, half * 32, a.q_scale);
-      store32_bf16(a.dqkv + (static_cast<long long>(b) * g.seq + tpos) * (3 * HD) + h * 64 + half * 32, v);
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        inv_rotary32(v, a.rot_t + tpos, a.rot_len, part * 32, a.q_scale);
+        store32_bf16(a.dqkv + (static_cast<long long>(b) * g.seq + tpos) * (3 * HD) + h * 64 + part * 32, v);
+      }
     }
   }
 
