@@ -7,6 +7,8 @@
 
 namespace b200 {
 
+int num_sms();  // gemm_sm100.cu
+
 constexpr int MAXV = 8;  // float4 chunks per lane: D <= 1024
 
 struct ShiftGeom {
@@ -39,205 +41,291 @@ __device__ __forceinline__ int shift_dst(const ShiftGeom& s, int t, int col, int
   return t;
 }
 
-// ------------------------------------------------------------------------------------------------
-// LayerNorm statistics: mean / rstd per row of x (or of 0.5*(x + x2))
-// ------------------------------------------------------------------------------------------------
-__global__ void ln_stats_kernel(const float* __restrict__ x, const float* __restrict__ x2, float* __restrict__ mean,
-                                float* __restrict__ rstd, int M, int D, float eps) {
-  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (row >= M) return;
-  const int nv = D / 128;
-  float4 v[MAXV];
-  float s = 0.f;
-#pragma unroll
-  for (int k = 0; k < MAXV; ++k) {
-    if (k < nv) {
-      const long long off = static_cast<long long>(row) * D + k * 128 + lane * 4;
-      v[k] = *reinterpret_cast<const float4*>(x + off);
-      if (x2) {
-        const float4 w = *reinterpret_cast<const float4*>(x2 + off);
-        v[k].x = 0.5f * (v[k].x + w.x); v[k].y = 0.5f * (v[k].y + w.y);
-        v[k].z = 0.5f * (v[k].z + w.z); v[k].w = 0.5f * (v[k].w + w.w);
-      }
-      s += v[k].x + v[k].y + v[k].z + v[k].w;
+// Per-row routing of the shift, computed once per row (the helpers above divide by the grid side on every call):
+// channels [0, D/4) of token t feed token dst[0], channels [D/4, D/2) feed dst[1], the rest stay (-1: dropped);
+// zero[q] tells that nothing shifts INTO quarter q of token t.
+struct ShiftRoute {
+  int dst[2];
+  bool zero[2];
+};
+// walks consecutive rows of the [B*seq] token matrix keeping (sample, token, grid row, grid column) without divisions
+struct RowWalk {
+  int row, bidx, t, ir, ic;
+  __device__ __forceinline__ void init(const ShiftGeom& s, int row0) {
+    row = row0;
+    bidx = row0 / s.seq;
+    t = row0 - bidx * s.seq;
+    const int p = t >= s.T ? t - s.T : 0;
+    ir = p / s.F;
+    ic = p - ir * s.F;
+  }
+  __device__ __forceinline__ void next(const ShiftGeom& s) {
+    ++row;
+    ++t;
+    if (t == s.seq) {
+      t = 0; ++bidx; ir = 0; ic = 0;
+    } else if (t > s.T) {
+      if (++ic == s.F) { ic = 0; ++ir; }
     }
   }
-  const float mu = warp_sum(s) / D;
-  float q = 0.f;
-#pragma unroll
-  for (int k = 0; k < MAXV; ++k) {
-    if (k < nv) {
-      const float a = v[k].x - mu, b = v[k].y - mu, c = v[k].z - mu, d = v[k].w - mu;
-      q += a * a + b * b + c * c + d * d;
-    }
+};
+__device__ __forceinline__ ShiftRoute shift_route(const ShiftGeom& s, const RowWalk& rw) {
+  ShiftRoute r;
+  const int t = rw.t;
+  if (!s.shift) {
+    r.dst[0] = r.dst[1] = t;
+    r.zero[0] = r.zero[1] = false;
+  } else if (t < s.T) {
+    r.dst[0] = r.dst[1] = (t + 1 < s.T) ? t + 1 : -1;
+    r.zero[0] = r.zero[1] = (t == 0);
+  } else {
+    r.dst[0] = (rw.ir + 1 < s.F && t + s.F < s.seq) ? t + s.F : -1;
+    r.dst[1] = (rw.ic + 1 < s.F && t + 1 < s.seq) ? t + 1 : -1;
+    r.zero[0] = rw.ir == 0;
+    r.zero[1] = rw.ic == 0;
   }
-  const float var = warp_sum(q) / D;
-  if (lane == 0) {
-    mean[row] = mu;
-    rstd[row] = rsqrtf(var + eps);
-  }
+  return r;
+}
+// row of the bf16 side (see ShiftGeom::split) as a 32-bit index
+__device__ __forceinline__ int permuted_row32(const ShiftGeom& s, int bidx, int t) {
+  if (s.split <= 0) return bidx * s.seq + t;
+  return t < s.split ? bidx * s.split + t : s.B * s.split + bidx * (s.seq - s.split) + (t - s.split);
 }
 
-// out[t, col] = LN(x)[src(t,col), col]  (bf16)
-__global__ void ln_shift_apply_kernel(const float* __restrict__ x, const float* __restrict__ x2,
-                                      const float* __restrict__ mean, const float* __restrict__ rstd,
-                                      const float* __restrict__ w, const float* __restrict__ b,
-                                      __nv_bfloat16* __restrict__ out, int M, int D, ShiftGeom sg) {
-  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (row >= M) return;
-  const int nv = D / 128;
-  const int bidx = row / sg.seq, t = row - bidx * sg.seq;
+// ------------------------------------------------------------------------------------------------
+// LayerNorm fused with the token shift, forward.  128 threads per SOURCE row: the row is read once, its statistics
+// are reduced in the group, and the normalised values are scattered to the rows the shift sends them to (each
+// output element has exactly one writer: its source row, or - where the shift pads with zeros - the row itself).
+// ------------------------------------------------------------------------------------------------
+constexpr int LNF_GROUPS = 4;
+__global__ void __launch_bounds__(128 * LNF_GROUPS, 2)
+ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, const float* __restrict__ w,
+                    const float* __restrict__ b, __nv_bfloat16* __restrict__ out, float* __restrict__ mean,
+                    float* __restrict__ rstd, int M, int D, float eps, ShiftGeom sg) {
+  // persistent blocks of 4 row groups x 128 threads (<= 8 channels per thread), each group walking a contiguous
+  // range of rows; the next row's loads are issued before the current row's reductions (two register buffers in
+  // ping-pong).  (A warp-per-row variant with 8 float4 per lane measured 1.8x slower: too few loads in flight.)
+  __shared__ float sred[LNF_GROUPS][2][2][4];   // [group][row parity][mean / var pass][warp]
+  const int grp = threadIdx.x >> 7, t128 = threadIdx.x & 127, wsub = t128 >> 5;
+  const int nper = D / 512;
+  bool act[2];
+  int colk[2], quarter[2];
+  float4 ww[2], bb[2];
 #pragma unroll
-  for (int k = 0; k < MAXV; ++k) {
-    if (k < nv) {
-      const int col = k * 128 + lane * 4;
-      const int st = shift_src(sg, t, col, D);
-      uint2 o = make_uint2(0u, 0u);
-      if (st >= 0) {
-        const long long srow = static_cast<long long>(bidx) * sg.seq + st;
-        float4 v = *reinterpret_cast<const float4*>(x + srow * D + col);
+  for (int k = 0; k < 2; ++k) {
+    colk[k] = k * 512 + t128 * 4;
+    quarter[k] = colk[k] < D / 4 ? 0 : (colk[k] < D / 2 ? 1 : 2);
+    act[k] = (k < nper) || (nper == 0 && k == 0 && colk[k] < D);
+    ww[k] = act[k] ? __ldg(reinterpret_cast<const float4*>(w + colk[k])) : make_float4(0.f, 0.f, 0.f, 0.f);
+    bb[k] = act[k] ? __ldg(reinterpret_cast<const float4*>(b + colk[k])) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  auto load_row = [&](int row, float4* v) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (act[k] && row < M) {
+        const long long off = static_cast<long long>(row) * D + colk[k];
+        v[k] = *reinterpret_cast<const float4*>(x + off);
         if (x2) {
-          const float4 u = *reinterpret_cast<const float4*>(x2 + srow * D + col);
-          v.x = 0.5f * (v.x + u.x); v.y = 0.5f * (v.y + u.y); v.z = 0.5f * (v.z + u.z); v.w = 0.5f * (v.w + u.w);
+          const float4 u = *reinterpret_cast<const float4*>(x2 + off);
+          v[k] = make_float4(0.5f * (v[k].x + u.x), 0.5f * (v[k].y + u.y), 0.5f * (v[k].z + u.z),
+                             0.5f * (v[k].w + u.w));
         }
-        const float mu = mean[srow], rs = rstd[srow];
-        const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
-        const float4 bb = __ldg(reinterpret_cast<const float4*>(b + col));
-        o.x = pack_bf16x2((v.x - mu) * rs * ww.x + bb.x, (v.y - mu) * rs * ww.y + bb.y);
-        o.y = pack_bf16x2((v.z - mu) * rs * ww.z + bb.z, (v.w - mu) * rs * ww.w + bb.w);
       }
-      *reinterpret_cast<uint2*>(out + permuted_row(sg, bidx, t) * D + col) = o;
+    }
+  };
+  const int groups_total = gridDim.x * LNF_GROUPS;
+  const int rows_per = (M + groups_total - 1) / groups_total;
+  const int row_begin = min(M, (blockIdx.x * LNF_GROUPS + grp) * rows_per), row_end = min(M, row_begin + rows_per);
+  RowWalk rw;
+  rw.init(sg, row_begin);
+  const float inv_d = 1.0f / D;
+  int it = 0;
+  auto process = [&](const float4* v) {
+    const int row = rw.row;
+    float* red = &sred[grp][it & 1][0][0];
+    float s = (v[0].x + v[0].y) + (v[0].z + v[0].w) + (v[1].x + v[1].y) + (v[1].z + v[1].w);
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[wsub] = s;
+    asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+    const float mu = ((red[0] + red[1]) + (red[2] + red[3])) * inv_d;
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      if (act[k]) {
+        const float a = v[k].x - mu, c = v[k].y - mu, d = v[k].z - mu, e = v[k].w - mu;
+        q += a * a + c * c + d * d + e * e;
+      }
+    }
+    q = warp_sum(q);
+    if ((threadIdx.x & 31) == 0) red[4 + wsub] = q;
+    asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+    const float rs = rsqrtf(((red[4] + red[5]) + (red[6] + red[7])) * inv_d + eps);
+    if (t128 == 0) {
+      mean[row] = mu;
+      rstd[row] = rs;
+    }
+    const ShiftRoute rt = shift_route(sg, rw);
+    const int r_self = permuted_row32(sg, rw.bidx, rw.t);
+    const float nmr = -mu * rs;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      if (act[k]) {
+        const int dtok = quarter[k] == 0 ? rt.dst[0] : (quarter[k] == 1 ? rt.dst[1] : rw.t);
+        if (dtok >= 0) {
+          uint2 o;
+          o.x = pack_bf16x2(fmaf(fmaf(v[k].x, rs, nmr), ww[k].x, bb[k].x), fmaf(fmaf(v[k].y, rs, nmr), ww[k].y, bb[k].y));
+          o.y = pack_bf16x2(fmaf(fmaf(v[k].z, rs, nmr), ww[k].z, bb[k].z), fmaf(fmaf(v[k].w, rs, nmr), ww[k].w, bb[k].w));
+          *reinterpret_cast<uint2*>(out + static_cast<long long>(permuted_row32(sg, rw.bidx, dtok)) * D + colk[k]) = o;
+        }
+        const bool z = quarter[k] == 0 ? rt.zero[0] : (quarter[k] == 1 ? rt.zero[1] : false);
+        if (z)   // nothing shifts into these channels of row t: they are zero
+          *reinterpret_cast<uint2*>(out + static_cast<long long>(r_self) * D + colk[k]) = make_uint2(0u, 0u);
+      }
+    }
+    ++it;
+  };
+  float4 va[2], vb[2];
+  if (row_begin < row_end) {   // (uniform per row group, and the group barriers are only used inside)
+    load_row(row_begin, va);
+    while (true) {
+      load_row(rw.row + 1 < row_end ? rw.row + 1 : M, vb);
+      process(va);
+      rw.next(sg);
+      if (rw.row >= row_end) break;
+      load_row(rw.row + 1 < row_end ? rw.row + 1 : M, va);
+      process(vb);
+      rw.next(sg);
+      if (rw.row >= row_end) break;
     }
   }
 }
 
-// Backward of shift(LN(x)).  dh: gradient of the shifted output (bf16).  Per row t: dn = gather of dh through the
-// transposed shift; dx = rstd * (w*dn - mean(w*dn) - xhat * mean(w*dn*xhat)).
+// Backward of shift(LN(x)), one pass.  dh: gradient of the shifted output (bf16).  Per row t: dn = gather of dh
+// through the transposed shift; dx = rstd * (w*dn - mean(w*dn) - xhat * mean(w*dn*xhat)).
 //   mode 0: dx_out[t] += dx           (reversible block: accumulate into the running stream gradient)
 //   mode 1: dx_out[t] = dx2_out[t] = 0.5 * dx   (final norm over the mean of the two streams)
-// Row kernel (4 warps per row -> 8 elements per thread, full occupancy) + column kernel for dw, db.
-__global__ void __launch_bounds__(256)
-ln_shift_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
-                       const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
-                       float* __restrict__ dx_out, float* __restrict__ dx2_out, int M, int D, ShiftGeom sg, int mode) {
-  __shared__ float sred[2][4][2];
-  const int sub = threadIdx.x >> 7;            // which of the block's 2 rows
+// Persistent blocks of 4 row groups x 128 threads: a group walks rows with a grid stride and a thread owns the same
+// <= 8 columns on every row, so dw / db accumulate in registers and leave through one shared-memory reduction +
+// global atomics per block.  All loads of a row (dh, x, the old dx) are issued before the first use.
+constexpr int LNB_GROUPS = 4;
+__global__ void __launch_bounds__(128 * LNB_GROUPS, 2)
+ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
+                    const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
+                    float* __restrict__ dx_out, float* __restrict__ dx2_out, float* __restrict__ dw,
+                    float* __restrict__ db, int M, int D, ShiftGeom sg, int mode) {
+  __shared__ float sred[LNB_GROUPS][2][4][2];   // [group][parity][warp][s1, s2]
+  __shared__ float s_acc[LNB_GROUPS - 1][2][128 * MAXV];
+  const int grp = threadIdx.x >> 7;            // row group of the block
   const int t128 = threadIdx.x & 127;          // thread inside the row group
-  const int wsub = t128 >> 5;                  // warp inside the row group
-  const int row = blockIdx.x * 2 + sub;
-  const bool live = row < M;
-  const int nper = D / 512;                    // float4 chunks per thread (D = 1024 -> 2, D = 512 -> 1)
-  const int rrow = live ? row : 0;
-  const int bidx = rrow / sg.seq, t = rrow - bidx * sg.seq;
-  const float mu = mean[rrow], rs = rstd[rrow];
-  float4 dn[2], xh[2];
-  float s1 = 0.f, s2 = 0.f;
+  const int wsub = t128 >> 5;
+  const int nper = D / 512;                    // float4 chunks per thread (D = 1024 -> 2, D = 512 -> 1, 256 -> half)
+  bool act[2];
+  int colk[2];
+  float4 ww[2];
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
-    const int col = k * 512 + t128 * 4;
-    if (k < nper || (nper == 0 && k == 0 && col < D)) {
-      const int dt = shift_dst(sg, t, col, D);
-      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (dt >= 0) {
-        const uint2 u = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
-        const float2 a = unpack_bf16x2(u.x), c = unpack_bf16x2(u.y);
-        g = make_float4(a.x, a.y, c.x, c.y);
+    colk[k] = k * 512 + t128 * 4;
+    act[k] = (k < nper) || (nper == 0 && k == 0 && colk[k] < D);
+    ww[k] = act[k] ? __ldg(reinterpret_cast<const float4*>(w + colk[k])) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  float4 aw[2], ab[2];
+  aw[0] = aw[1] = ab[0] = ab[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int groups_total = gridDim.x * LNB_GROUPS;
+  const int rows_per = (M + groups_total - 1) / groups_total;   // every row group owns a contiguous range of rows
+  const int row_begin = min(M, (blockIdx.x * LNB_GROUPS + grp) * rows_per), row_end = min(M, row_begin + rows_per);
+  RowWalk rw;
+  rw.init(sg, row_begin);
+  for (int it = 0; rw.row < row_end; rw.next(sg), ++it) {
+    const int row = rw.row;
+    const ShiftRoute rt = shift_route(sg, rw);
+    const long long r_self = static_cast<long long>(permuted_row32(sg, rw.bidx, rw.t)) * D;
+    const long long r_q0 = rt.dst[0] >= 0 ? static_cast<long long>(permuted_row32(sg, rw.bidx, rt.dst[0])) * D : -1;
+    const long long r_q1 = rt.dst[1] >= 0 ? static_cast<long long>(permuted_row32(sg, rw.bidx, rt.dst[1])) * D : -1;
+    const float mu = mean[row], rs = rstd[row];
+    uint2 u[2];
+    float4 v[2], v2[2], old[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      u[k] = make_uint2(0u, 0u);
+      v[k] = v2[k] = old[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (act[k]) {
+        const int col = colk[k];
+        const long long src = col < D / 4 ? r_q0 : (col < D / 2 ? r_q1 : r_self);
+        if (src >= 0) u[k] = *reinterpret_cast<const uint2*>(dh + src + col);
+        v[k] = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
+        if (x2) v2[k] = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
+        if (mode == 0) old[k] = *reinterpret_cast<const float4*>(dx_out + static_cast<long long>(row) * D + col);
       }
-      float4 v = *reinterpret_cast<const float4*>(x + static_cast<long long>(rrow) * D + col);
-      if (x2) {
-        const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(rrow) * D + col);
-        v.x = 0.5f * (v.x + u2.x); v.y = 0.5f * (v.y + u2.y); v.z = 0.5f * (v.z + u2.z); v.w = 0.5f * (v.w + u2.w);
-      }
-      const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
-      xh[k] = make_float4((v.x - mu) * rs, (v.y - mu) * rs, (v.z - mu) * rs, (v.w - mu) * rs);
-      dn[k] = make_float4(g.x * ww.x, g.y * ww.y, g.z * ww.z, g.w * ww.w);
+    }
+    float4 dn[2], xh[2];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const float2 a = unpack_bf16x2(u[k].x), c = unpack_bf16x2(u[k].y);
+      float4 vv = v[k];
+      if (x2) vv = make_float4(0.5f * (vv.x + v2[k].x), 0.5f * (vv.y + v2[k].y), 0.5f * (vv.z + v2[k].z),
+                               0.5f * (vv.w + v2[k].w));
+      xh[k] = act[k] ? make_float4((vv.x - mu) * rs, (vv.y - mu) * rs, (vv.z - mu) * rs, (vv.w - mu) * rs)
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+      aw[k].x += a.x * xh[k].x; aw[k].y += a.y * xh[k].y; aw[k].z += c.x * xh[k].z; aw[k].w += c.y * xh[k].w;
+      ab[k].x += a.x; ab[k].y += a.y; ab[k].z += c.x; ab[k].w += c.y;
+      dn[k] = make_float4(a.x * ww[k].x, a.y * ww[k].y, c.x * ww[k].z, c.y * ww[k].w);
       s1 += dn[k].x + dn[k].y + dn[k].z + dn[k].w;
       s2 += dn[k].x * xh[k].x + dn[k].y * xh[k].y + dn[k].z * xh[k].z + dn[k].w * xh[k].w;
-    } else {
-      dn[k] = xh[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-  }
-  s1 = warp_sum(s1);
-  s2 = warp_sum(s2);
-  if ((threadIdx.x & 31) == 0) { sred[sub][wsub][0] = s1; sred[sub][wsub][1] = s2; }
-  __syncthreads();
-  s1 = (sred[sub][0][0] + sred[sub][1][0] + sred[sub][2][0] + sred[sub][3][0]) / D;
-  s2 = (sred[sub][0][1] + sred[sub][1][1] + sred[sub][2][1] + sred[sub][3][1]) / D;
-  if (!live) return;
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    float* red = &sred[grp][it & 1][0][0];
+    if ((threadIdx.x & 31) == 0) { red[wsub * 2] = s1; red[wsub * 2 + 1] = s2; }
+    asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");   // the row group's own barrier
+    s1 = (red[0] + red[2] + red[4] + red[6]) / D;
+    s2 = (red[1] + red[3] + red[5] + red[7]) / D;
 #pragma unroll
-  for (int k = 0; k < 2; ++k) {
-    const int col = k * 512 + t128 * 4;
-    if (k < nper || (nper == 0 && k == 0 && col < D)) {
-      float4 d;
-      d.x = rs * (dn[k].x - s1 - xh[k].x * s2);
-      d.y = rs * (dn[k].y - s1 - xh[k].y * s2);
-      d.z = rs * (dn[k].z - s1 - xh[k].z * s2);
-      d.w = rs * (dn[k].w - s1 - xh[k].w * s2);
-      float4* p = reinterpret_cast<float4*>(dx_out + static_cast<long long>(row) * D + col);
-      if (mode == 0) {
-        const float4 o = *p;
-        *p = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w);
-      } else {
-        const float4 hlf = make_float4(0.5f * d.x, 0.5f * d.y, 0.5f * d.z, 0.5f * d.w);
-        *p = hlf;
-        *reinterpret_cast<float4*>(dx2_out + static_cast<long long>(row) * D + col) = hlf;
-      }
-    }
-  }
-}
-
-// dw[col] += sum_rows dn*xhat ; db[col] += sum_rows dn.  thread = 4 columns, block = one row slice; 4 rows in flight.
-__global__ void __launch_bounds__(256)
-ln_shift_bwd_dwdb_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x,
-                         const float* __restrict__ x2, const float* __restrict__ mean, const float* __restrict__ rstd,
-                         float* __restrict__ dw, float* __restrict__ db, int M, int D, ShiftGeom sg) {
-  const int cols_per_block = blockDim.x * 4;
-  const int stripes = D / cols_per_block;
-  const int col = (blockIdx.x % stripes) * cols_per_block + threadIdx.x * 4;
-  const int rsplit = blockIdx.x / stripes, nsplit = gridDim.x / stripes;
-  const int rows_per = (M + nsplit - 1) / nsplit;
-  const int r0 = rsplit * rows_per, r1 = min(M, r0 + rows_per);
-  float4 aw = make_float4(0.f, 0.f, 0.f, 0.f), ab = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int base = r0; base < r1; base += 4) {
-    uint2 u[4];
-    float4 v[4];
-    float mu[4], rs[4];
-    bool ok[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int row = base + j;
-      ok[j] = false;
-      u[j] = make_uint2(0u, 0u);
-      v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-      mu[j] = 0.f; rs[j] = 0.f;
-      if (row < r1) {
-        const int bidx = row / sg.seq, t = row - bidx * sg.seq;
-        const int dt = shift_dst(sg, t, col, D);
-        if (dt >= 0) {
-          ok[j] = true;
-          u[j] = *reinterpret_cast<const uint2*>(dh + permuted_row(sg, bidx, dt) * D + col);
-          v[j] = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
-          if (x2) {
-            const float4 u2 = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
-            v[j] = make_float4(0.5f * (v[j].x + u2.x), 0.5f * (v[j].y + u2.y), 0.5f * (v[j].z + u2.z), 0.5f * (v[j].w + u2.w));
-          }
-          mu[j] = mean[row];
-          rs[j] = rstd[row];
+    for (int k = 0; k < 2; ++k) {
+      if (act[k]) {
+        float4 d;
+        d.x = rs * (dn[k].x - s1 - xh[k].x * s2);
+        d.y = rs * (dn[k].y - s1 - xh[k].y * s2);
+        d.z = rs * (dn[k].z - s1 - xh[k].z * s2);
+        d.w = rs * (dn[k].w - s1 - xh[k].w * s2);
+        float4* p = reinterpret_cast<float4*>(dx_out + static_cast<long long>(row) * D + colk[k]);
+        if (mode == 0) {
+          *p = make_float4(old[k].x + d.x, old[k].y + d.y, old[k].z + d.z, old[k].w + d.w);
+        } else {
+          const float4 hlf = make_float4(0.5f * d.x, 0.5f * d.y, 0.5f * d.z, 0.5f * d.w);
+          *p = hlf;
+          *reinterpret_cast<float4*>(dx2_out + static_cast<long long>(row) * D + colk[k]) = hlf;
         }
       }
     }
+  }
+  // block reduction of dw / db: groups 1.. park their partials in shared memory, group 0 adds and publishes
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (ok[j]) {
-        const float2 a = unpack_bf16x2(u[j].x), c = unpack_bf16x2(u[j].y);
-        aw.x += a.x * (v[j].x - mu[j]) * rs[j]; aw.y += a.y * (v[j].y - mu[j]) * rs[j];
-        aw.z += c.x * (v[j].z - mu[j]) * rs[j]; aw.w += c.y * (v[j].w - mu[j]) * rs[j];
-        ab.x += a.x; ab.y += a.y; ab.z += c.x; ab.w += c.y;
+  for (int k = 0; k < 2; ++k) {
+    if (act[k] && grp > 0) {
+      *reinterpret_cast<float4*>(&s_acc[grp - 1][0][colk[k]]) = aw[k];
+      *reinterpret_cast<float4*>(&s_acc[grp - 1][1][colk[k]]) = ab[k];
+    }
+  }
+  __syncthreads();
+  if (grp == 0) {
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      if (act[k]) {
+        for (int g2 = 0; g2 < LNB_GROUPS - 1; ++g2) {
+          const float4 pw = *reinterpret_cast<const float4*>(&s_acc[g2][0][colk[k]]);
+          const float4 pb = *reinterpret_cast<const float4*>(&s_acc[g2][1][colk[k]]);
+          aw[k].x += pw.x; aw[k].y += pw.y; aw[k].z += pw.z; aw[k].w += pw.w;
+          ab[k].x += pb.x; ab[k].y += pb.y; ab[k].z += pb.z; ab[k].w += pb.w;
+        }
+        float* pw = dw + colk[k];
+        float* pb = db + colk[k];
+        atomicAdd(pw, aw[k].x); atomicAdd(pw + 1, aw[k].y); atomicAdd(pw + 2, aw[k].z); atomicAdd(pw + 3, aw[k].w);
+        atomicAdd(pb, ab[k].x); atomicAdd(pb + 1, ab[k].y); atomicAdd(pb + 2, ab[k].z); atomicAdd(pb + 3, ab[k].w);
       }
     }
   }
-  atomicAdd(dw + col, aw.x); atomicAdd(dw + col + 1, aw.y); atomicAdd(dw + col + 2, aw.z); atomicAdd(dw + col + 3, aw.w);
-  atomicAdd(db + col, ab.x); atomicAdd(db + col + 1, ab.y); atomicAdd(db + col + 2, ab.z); atomicAdd(db + col + 3, ab.w);
 }
 
 // d_o = bf16(dy * scale); dscale += colsum(dy * o); dbias += colsum(dy * scale).   thread = 4 columns
@@ -435,13 +523,13 @@ extern "C" int b200_ln_shift_fwd(const float* x, const float* x2, const float* w
                                  float* mean, float* rstd, int M, int D, int seq, int T, int F, int shift,
                                  int row_split, float eps, void* stream) {
   if (D % 128 || D > 128 * MAXV) return -41;
+  if (D % 512 && D != 256) return -41;  // 4 warps per row: D in {256, 512, 1024}
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  const int threads = 256, rows_per_block = threads / 32;
-  const int blocks = (M + rows_per_block - 1) / rows_per_block;
-  ln_stats_kernel<<<blocks, threads, 0, st>>>(x, x2, mean, rstd, M, D, eps);
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
-  ln_shift_apply_kernel<<<blocks, threads, 0, st>>>(x, x2, mean, rstd, w, b, reinterpret_cast<__nv_bfloat16*>(out), M,
-                                                    D, sg);
+  int blocks = num_sms() * 2;   // persistent: two 16-warp blocks per SM
+  if (blocks * LNF_GROUPS > M) blocks = (M + LNF_GROUPS - 1) / LNF_GROUPS;
+  ln_shift_fwd_kernel<<<blocks, 128 * LNF_GROUPS, 0, st>>>(x, x2, w, b, reinterpret_cast<__nv_bfloat16*>(out), mean,
+                                                           rstd, M, D, eps, sg);
   return err();
 }
 
@@ -452,17 +540,10 @@ extern "C" int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
   if (D % 512 && D != 256) return -41;  // 4 warps per row: D in {256, 512, 1024}
-  const int threads = 256;
-  const int blocks = (M + 1) / 2;
-  ln_shift_bwd_dx_kernel<<<blocks, threads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2, mean, rstd, w,
-                                                     dx, dx2, M, D, sg, mode);
-  int cthreads = 256;
-  if (D < cthreads * 4) cthreads = D / 4;
-  const int stripes = D / (cthreads * 4);
-  int nsplit = (148 * 8) / stripes;
-  if (nsplit > M) nsplit = M;
-  ln_shift_bwd_dwdb_kernel<<<stripes * nsplit, cthreads, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2,
-                                                                  mean, rstd, dw, db, M, D, sg);
+  int blocks = num_sms() * 2;   // persistent: two 16-warp blocks per SM
+  if (blocks * LNB_GROUPS > M) blocks = (M + LNB_GROUPS - 1) / LNB_GROUPS;
+  ln_shift_bwd_kernel<<<blocks, 128 * LNB_GROUPS, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2, mean, rstd, w, dx, dx2,
+                                              dw, db, M, D, sg, mode);
   return err();
 }
 

@@ -20,6 +20,7 @@ def test_greedy_decode_matches_oracle():
     from dalle_b200.models.decode_engine import DecodeEngine
 
     cfg = _cfg()
+    torch.manual_seed(0)   # the prompt is random: an unseeded draw occasionally lands on a near-tie argmax
     model = DALLE(cfg, seed=0)
     with torch.no_grad():
         for p in list(model.scale_f) + list(model.scale_g):

@@ -7,7 +7,7 @@ from dalle_b200.ops import attention as A, elementwise as E, gemm as G
 from dalle_b200.models.rotary import rotary_pair_table
 
 
-def timeit(fn, iters=10):
+def timeit(fn, iters=30):
     for _ in range(3): fn()
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(True), torch.cuda.Event(True)
