@@ -28,10 +28,13 @@ constexpr int GEMM_THREADS = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64B-swizzled TMA-store box
 constexpr int OUT_TILES_PER_WARP = 3;
 constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
-__host__ __device__ constexpr int gemm_stages(int epi) { return epi == B200_EPI_GEGLU ? 3 : 4; }
-__host__ __device__ constexpr int gemm_out_stage_bytes(int epi) {
-  return epi == B200_EPI_GEGLU ? OUT_STAGE_BYTES : (OUT_STAGE_BYTES * 2) / 3;  // 3 tiles/warp only for GEGLU
+__host__ __device__ constexpr int gemm_stages(int epi) {
+  return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD) ? 3 : 4;
 }
+__host__ __device__ constexpr int gemm_out_tiles(int epi) {   // staging tiles per epilogue warp
+  return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? 4 : 2);
+}
+__host__ __device__ constexpr int gemm_out_stage_bytes(int epi) { return 8 * gemm_out_tiles(epi) * OUT_TILE_BYTES; }
 __host__ __device__ constexpr int gemm_smem_bytes(int epi) {
   return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 256 /*barriers*/;
 }
@@ -58,16 +61,58 @@ struct GemmDev {
   float alpha;
 };
 
-// GELU pieces shared by forward and backward epilogues.  erff() is a pure FMA-pipe polynomial for the common range;
-// a measured A/B against an exp+rcp (MUFU) formulation showed the MUFU version 10-20% slower in these epilogues.
+// GELU pieces shared by forward and backward epilogues.  Phi(g) through Abramowitz-Stegun 7.1.26
+//   erf(x) = 1 - (a1 t + ... + a5 t^5) exp(-x^2),  t = 1 / (1 + p x),  x >= 0        (|error| <= 1.5e-7)
+// with x = |g| / sqrt(2): the exponential is exp(-g^2 / 2), i.e. the same one the density needs, so the pair costs
+// two MUFU ops (ex2, rcp) and ~12 FMA-pipe instructions; erff() + __expf() is ~40 and made these epilogues the
+// bottleneck of the FF GEMMs (8 epilogue warps cannot hide that much dependent math behind a K=1024 mainloop).
 struct GeluParts { float cdf, pdf; };
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ GeluParts gelu_parts(float g) {
+  const float ag = fabsf(g);
+  const float e = ex2_approx(g * g * -0.72134752044448170f);           // exp(-g^2 / 2)
+  const float t = rcp_approx(fmaf(ag, 0.3275911f * 0.70710678118654752f, 1.0f));
+  float p = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);        // 0.5 folded into the coefficients
+  p = fmaf(t, p, 0.5f * 1.421413741f);
+  p = fmaf(t, p, 0.5f * -0.284496736f);
+  p = fmaf(t, p, 0.5f * 0.254829592f);
+  const float tail = p * t * e;                                         // 1 - Phi(|g|)
   GeluParts r;
-  r.cdf = 0.5f * (1.0f + erff(g * 0.70710678118654752f));
-  r.pdf = 0.3989422804014327f * __expf(-0.5f * g * g);
+  r.cdf = g >= 0.f ? 1.0f - tail : tail;
+  r.pdf = 0.3989422804014327f * e;
   return r;
 }
-__device__ __forceinline__ float gelu_cdf(float g) { return 0.5f * (1.0f + erff(g * 0.70710678118654752f)); }
+// Two elements at a time on the packed fp32x2 FMA path of sm_100 (FFMA2 / FMUL2 / FADD2 halve the FMA-pipe issue
+// slots of the polynomial; MUFU and the sign handling stay scalar).
+struct GeluParts2 { float2 cdf, pdf; };
+__device__ __forceinline__ float2 splat2(float x) { return make_float2(x, x); }
+__device__ __forceinline__ GeluParts2 gelu_parts2(float2 g) {
+  const float2 arg = __fmul2_rn(__fmul2_rn(g, g), splat2(-0.72134752044448170f));
+  const float2 e = make_float2(ex2_approx(arg.x), ex2_approx(arg.y));
+  const float2 den = __ffma2_rn(make_float2(fabsf(g.x), fabsf(g.y)), splat2(0.3275911f * 0.70710678118654752f),
+                                splat2(1.0f));
+  const float2 t = make_float2(rcp_approx(den.x), rcp_approx(den.y));
+  float2 p = __ffma2_rn(t, splat2(0.5f * 1.061405429f), splat2(0.5f * -1.453152027f));
+  p = __ffma2_rn(t, p, splat2(0.5f * 1.421413741f));
+  p = __ffma2_rn(t, p, splat2(0.5f * -0.284496736f));
+  p = __ffma2_rn(t, p, splat2(0.5f * 0.254829592f));
+  const float2 tail = __fmul2_rn(__fmul2_rn(p, t), e);                 // 1 - Phi(|g|), in (0, 0.5]
+  const float2 h = __ffma2_rn(tail, splat2(-1.0f), splat2(0.5f));      // Phi(|g|) - 0.5 >= 0
+  GeluParts2 r;
+  r.cdf = __fadd2_rn(splat2(0.5f), make_float2(copysignf(h.x, g.x), copysignf(h.y, g.y)));
+  r.pdf = __fmul2_rn(e, splat2(0.3989422804014327f));
+  return r;
+}
+__device__ __forceinline__ float gelu_cdf(float g) { return gelu_parts(g).cdf; }
 __device__ __forceinline__ float gelu_erf(float x) { return x * gelu_cdf(x); }
 
 __device__ __forceinline__ void st_bf16x8(__nv_bfloat16* p, const float* v) {
@@ -121,6 +166,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* aux_bar = bars + 2 * STAGES + 6;     // [8 warps][2 sets], GEGLU_BWD only: TMA loads of the aux tiles
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -136,6 +182,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 256);
     }
+    if (EPI == B200_EPI_GEGLU_BWD)
+      for (int s = 0; s < 16; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -226,7 +274,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ------------------------------- epilogue warps -------------------------------------------
     const int q = warp & 3;
     const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
-    constexpr int TILES = (EPI == B200_EPI_GEGLU) ? 3 : 2;
+    constexpr int TILES = gemm_out_tiles(EPI);
     uint8_t* stage = smem_out + (warp - 2) * TILES * OUT_TILE_BYTES;
     // bf16 outputs leave through smem: 32 rows x 32 columns per warp and chunk, 64B-swizzled, one TMA store each
     // (full 32-byte sectors instead of 32 scattered 16-byte row pieces per store instruction)
@@ -253,6 +301,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     auto stage_commit = [&]() {
       if (lane == 0) tma_store_commit();
     };
+    uint64_t* my_aux_bar = aux_bar + (warp - 2) * 2;
+    uint32_t aux_n = 0;   // chunks consumed so far: set = aux_n & 1, mbarrier parity = (aux_n >> 1) & 1
+    auto aux_load = [&](int set, int x, int y) {   // one lane: both aux tiles of a chunk -> staging set
+      uint8_t* dst = stage + (2 * set) * OUT_TILE_BYTES;
+      mbar_expect_tx(&my_aux_bar[set], 2 * OUT_TILE_BYTES);
+      tma_load_2d(dst, &tmO2, &my_aux_bar[set], x, y);
+      tma_load_2d(dst + OUT_TILE_BYTES, &tmO2, &my_aux_bar[set], g.n_half + x, y);
+    };
+    if (EPI == B200_EPI_GEGLU_BWD && blockIdx.x < units && lane == 0) {
+      const int t0 = blockIdx.x / g.splits;
+      const int x0 = (t0 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+      if (x0 < g.N) aux_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
+    }
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -277,11 +338,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (col < g.n_half) {  // warp-uniform
             float va[32], vg[32], o[32];
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const bool cok = col + j < g.n_half;
-              va[j] = __uint_as_float(ra[j]) + ((g.bias && cok) ? __ldg(g.bias + col + j) : 0.f);
-              vg[j] = __uint_as_float(rg[j]) + ((g.bias && cok) ? __ldg(g.bias + g.n_half + col + j) : 0.f);
-              o[j] = va[j] * gelu_erf(vg[j]);
+            for (int j = 0; j < 32; j += 2) {
+              const bool c0 = g.bias && col + j < g.n_half, c1 = g.bias && col + j + 1 < g.n_half;
+              const float2 ba = make_float2(c0 ? __ldg(g.bias + col + j) : 0.f, c1 ? __ldg(g.bias + col + j + 1) : 0.f);
+              const float2 bg = make_float2(c0 ? __ldg(g.bias + g.n_half + col + j) : 0.f,
+                                            c1 ? __ldg(g.bias + g.n_half + col + j + 1) : 0.f);
+              const float2 a2 = __fadd2_rn(make_float2(__uint_as_float(ra[j]), __uint_as_float(ra[j + 1])), ba);
+              const float2 g2 = __fadd2_rn(make_float2(__uint_as_float(rg[j]), __uint_as_float(rg[j + 1])), bg);
+              const float2 o2 = __fmul2_rn(__fmul2_rn(a2, g2), gelu_parts2(g2).cdf);
+              va[j] = a2.x; va[j + 1] = a2.y;
+              vg[j] = g2.x; vg[j + 1] = g2.y;
+              o[j] = o2.x; o[j + 1] = o2.y;
             }
             const int y = m_blk * BM + q * 32;
             stage_reuse();
@@ -294,6 +361,68 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             stage_commit();
           }
         }
+      } else if (EPI == B200_EPI_GEGLU_BWD) {
+        // acc = d(geglu out); aux = [value_pre | gate_pre] (bf16).  The aux tiles of a chunk arrive by TMA in the
+        // warp's staging buffers (two sets in ping-pong; per-lane row loads would cost 32 L1 wavefronts per
+        // instruction), are turned into (d value, d gate) in place and leave through TMA stores.
+        const int y = m_blk * BM + q * 32;
+#pragma unroll 1
+        for (int ci = 0; ci < BN / 64; ++ci) {
+          const int c = chalf * (BN / 64) + ci;
+          const int col = n0 + c * 32;
+          {   // prefetch the next chunk (of this tile, or the first of the CTA's next tile) into the other set
+            int ncol = col + 32, ny = y;
+            bool have = ci + 1 < BN / 64;
+            if (!have) {
+              const int u2 = u + gridDim.x;
+              have = u2 < units;
+              const int t2 = u2 / g.splits;
+              ncol = (t2 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+              ny = (t2 / g.n_tiles) * BM + q * 32;
+            }
+            if (have && ncol < g.N) {
+              stage_reuse();   // the stores that read that set (two chunks ago) are done with it
+              if (lane == 0) aux_load((aux_n + 1) & 1, ncol, ny);
+            }
+          }
+          if (col >= g.N) continue;  // warp-uniform (never prefetched either)
+          const int set = aux_n & 1;
+          mbar_wait(&my_aux_bar[set], (aux_n >> 1) & 1);
+          ++aux_n;
+          uint32_t r[32];
+          tmem_ld32(taddr + c * 32, r);
+          tmem_ld_wait();
+          const uint8_t* ta_ = stage + (2 * set) * OUT_TILE_BYTES + lane * 64;
+          const uint8_t* tg_ = ta_ + OUT_TILE_BYTES;
+          const int sw = (lane >> 1) & 3;
+          float da[32], dg[32];
+#pragma unroll
+          for (int p8 = 0; p8 < 4; ++p8) {
+            const uint4 ua = *reinterpret_cast<const uint4*>(ta_ + ((p8 ^ sw) << 4));
+            const uint4 ug = *reinterpret_cast<const uint4*>(tg_ + ((p8 ^ sw) << 4));
+            const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wg[4] = {ug.x, ug.y, ug.z, ug.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int j = p8 * 8 + e * 2;
+              const float2 a2 = unpack_bf16x2(wa[e]), g2 = unpack_bf16x2(wg[e]);
+              const float2 v2 = row_ok ? make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]))
+                                       : make_float2(0.f, 0.f);
+              const GeluParts2 gp = gelu_parts2(g2);
+              const float2 x = __fmul2_rn(__fmul2_rn(v2, g2), gp.cdf);
+              const float2 y2 = __fmul2_rn(__fmul2_rn(v2, a2), __ffma2_rn(g2, gp.pdf, gp.cdf));
+              da[j] = x.x; da[j + 1] = x.y;
+              dg[j] = y2.x; dg[j + 1] = y2.y;
+            }
+          }
+          __syncwarp();
+          stage_write(2 * set, da);
+          stage_write(2 * set + 1, dg);
+          fence_proxy_async_smem();
+          __syncwarp();
+          stage_flush(&tmO, 2 * set, col, y);
+          stage_flush(&tmO, 2 * set + 1, g.n_half + col, y);
+          stage_commit();
+        }
       } else {
 #pragma unroll 1
         for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
@@ -302,7 +431,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint32_t r[32];
           tmem_ld32(taddr + c * 32, r);
           tmem_ld_wait();
-          constexpr bool kStaged = (EPI == B200_EPI_BF16 || EPI == B200_EPI_ROTARY || EPI == B200_EPI_GEGLU_BWD);
+          constexpr bool kStaged = (EPI == B200_EPI_BF16 || EPI == B200_EPI_ROTARY);
           if (!kStaged && !row_ok) continue;   // staged epilogues keep the warp converged; TMA clips the tails
           const int y = m_blk * BM + q * 32;
           float v[32];
@@ -376,48 +505,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if (g.out2)
               store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2, col, g.N, v);
-          } else if (EPI == B200_EPI_GEGLU_BWD) {
-            if (!row_ok) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = 0.f;
-            }
-            // acc = d(geglu out); aux = [value_pre | gate_pre] (bf16, ld = ldaux)
-            const __nv_bfloat16* ap = g.aux + (long long)(row_ok ? row : 0) * g.ldaux + col;
-            float da[32], dg[32];
-            if (full) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                float a8[8], g8[8];
-                ld_bf16x8(ap + j, a8);
-                ld_bf16x8(ap + g.n_half + j, g8);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                  const GeluParts gp = gelu_parts(g8[e]);
-                  da[j + e] = v[j + e] * g8[e] * gp.cdf;
-                  dg[j + e] = v[j + e] * a8[e] * fmaf(g8[e], gp.pdf, gp.cdf);
-                }
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                if (col + j < g.N) {
-                  const float a = __bfloat162float(ap[j]), gg = __bfloat162float(ap[g.n_half + j]);
-                  const GeluParts gp = gelu_parts(gg);
-                  da[j] = v[j] * gg * gp.cdf;
-                  dg[j] = v[j] * a * fmaf(gg, gp.pdf, gp.cdf);
-                } else {
-                  da[j] = dg[j] = 0.f;
-                }
-              }
-            }
-            stage_reuse();
-            stage_write(0, da);
-            stage_write(1, dg);
-            fence_proxy_async_smem();
-            __syncwarp();
-            stage_flush(&tmO, 0, col, y);
-            stage_flush(&tmO, 1, g.n_half + col, y);
-            stage_commit();
           } else if (EPI == B200_EPI_ATOMIC_F32) {
             float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
             if (full) {
@@ -628,6 +715,11 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
                              : (d->epi == B200_EPI_GEGLU_BWD ? (uint64_t)2 * d->n_half : (uint64_t)d->N);
       rc = make_tmap_bf16_out(&g_tm_out, d->out, d->M, ocols, d->ldo);
       if (rc) return rc;
+      if (d->epi == B200_EPI_GEGLU_BWD) {   // the aux operand is read through the second map
+        if ((d->ldaux % 8) || reinterpret_cast<uintptr_t>(d->aux) % 16) return -15;
+        rc = make_tmap_bf16_out(&g_tm_out2, d->aux, d->M, (uint64_t)2 * d->n_half, d->ldaux);
+        if (rc) return rc;
+      }
       if (d->epi == B200_EPI_GEGLU && d->out2) {
         if ((d->ldo2 % 8) || reinterpret_cast<uintptr_t>(d->out2) % 16) return -15;
         rc = make_tmap_bf16_out(&g_tm_out2, d->out2, d->M, (uint64_t)2 * d->n_half, d->ldo2);

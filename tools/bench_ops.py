@@ -17,7 +17,15 @@ def timeit(fn, iters=30):
     return s.elapsed_time(e) / iters * 1e3  # us
 
 
+def box_speed():
+    """cuBLAS bf16 8192^3 matmul TF/s: a yardstick for the box's current power/clock state."""
+    a = torch.randn(8192, 8192, device='cuda', dtype=torch.bfloat16); b = torch.randn(8192, 8192, device='cuda', dtype=torch.bfloat16)
+    t = timeit(lambda: torch.matmul(a, b), iters=20)
+    return 2 * 8192 ** 3 / t / 1e6
+
+
 def main():
+    print(f"box speed (cuBLAS 8192^3): {box_speed():.0f} TF/s", flush=True)
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
     cfg = ttt_config()
     M, D, I = B * cfg.seq_len, cfg.dim, cfg.inner_dim
@@ -66,6 +74,9 @@ def main():
     gWo = torch.zeros(D, D, device=dev)
     t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, d_o, h, gWo))
     print(f"wgrad 1024x1024  {t_:.0f} us  {2*M*D*D/t_/1e6:.0f} TF/s")
+
+
+    print(f"box speed (cuBLAS 8192^3): {box_speed():.0f} TF/s", flush=True)
 
 
 if __name__ == "__main__":
