@@ -29,10 +29,10 @@ constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64
 constexpr int OUT_TILES_PER_WARP = 3;
 constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
 __host__ __device__ constexpr int gemm_stages(int epi) {
-  return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD) ? 3 : 4;
+  return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;
 }
 __host__ __device__ constexpr int gemm_out_tiles(int epi) {   // staging tiles per epilogue warp
-  return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? 4 : 2);
+  return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? 4 : (epi == B200_EPI_RESID ? 5 : 2));
 }
 __host__ __device__ constexpr int gemm_out_stage_bytes(int epi) { return 8 * gemm_out_tiles(epi) * OUT_TILE_BYTES; }
 __host__ __device__ constexpr int gemm_smem_bytes(int epi) {
@@ -151,7 +151,8 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* rowp, int col, int
 template <int A_MN, int B_MN, int EPI>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2, const GemmDev g) {
+            const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2,
+            const __grid_constant__ CUtensorMap tmX, const GemmDev g) {
   constexpr int STAGES = gemm_stages(EPI);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
@@ -166,7 +167,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-  uint64_t* aux_bar = bars + 2 * STAGES + 6;     // [8 warps][2 sets], GEGLU_BWD only: TMA loads of the aux tiles
+  uint64_t* aux_bar = bars + 2 * STAGES + 6;     // [8 warps][2 sets]: TMA loads of epilogue inputs (aux / residual)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -182,7 +183,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 256);
     }
-    if (EPI == B200_EPI_GEGLU_BWD)
+    if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID)
       for (int s = 0; s < 16; ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
@@ -309,10 +310,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       tma_load_2d(dst, &tmO2, &my_aux_bar[set], x, y);
       tma_load_2d(dst + OUT_TILE_BYTES, &tmO2, &my_aux_bar[set], g.n_half + x, y);
     };
-    if (EPI == B200_EPI_GEGLU_BWD && blockIdx.x < units && lane == 0) {
+    auto res_load = [&](int set, int x, int y) {   // one lane: the fp32 residual tile of a chunk -> staging set
+      mbar_expect_tx(&my_aux_bar[set], 2 * OUT_TILE_BYTES);
+      tma_load_2d(stage + (2 * set) * OUT_TILE_BYTES, &tmX, &my_aux_bar[set], x, y);
+    };
+    if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID) && blockIdx.x < units && lane == 0) {
       const int t0 = blockIdx.x / g.splits;
       const int x0 = (t0 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
-      if (x0 < g.N) aux_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
+      if (x0 < g.N) {
+        if (EPI == B200_EPI_RESID) res_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
+        else aux_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
+      }
     }
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -423,6 +431,64 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           stage_flush(&tmO, 2 * set + 1, g.n_half + col, y);
           stage_commit();
         }
+      } else if (EPI == B200_EPI_RESID) {
+        // out = res + alpha * scale[col] * (acc + bias[col]); optional bf16 copy of (acc + bias).
+        // The fp32 residual tile of a chunk (32 x 32, 128B-swizzled) arrives by TMA in the warp's staging buffers
+        // (two sets in ping-pong, fetched one chunk ahead), is updated in place and leaves through a TMA store:
+        // full-line traffic instead of 32 row pieces per load/store instruction, and no load-behind-store
+        // serialisation when `res` is `out` (the in-place residual stream).
+        const int y = m_blk * BM + q * 32;
+#pragma unroll 1
+        for (int ci = 0; ci < BN / 64; ++ci) {
+          const int c = chalf * (BN / 64) + ci;
+          const int col = n0 + c * 32;
+          {
+            int ncol = col + 32, ny = y;
+            bool have = ci + 1 < BN / 64;
+            if (!have) {
+              const int u2 = u + gridDim.x;
+              have = u2 < units;
+              const int t2 = u2 / g.splits;
+              ncol = (t2 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+              ny = (t2 / g.n_tiles) * BM + q * 32;
+            }
+            if (have && ncol < g.N) {
+              stage_reuse();
+              if (lane == 0) res_load((aux_n + 1) & 1, ncol, ny);
+            }
+          }
+          if (col >= g.N) continue;  // warp-uniform (never prefetched either)
+          const int set = aux_n & 1;
+          mbar_wait(&my_aux_bar[set], (aux_n >> 1) & 1);
+          ++aux_n;
+          uint32_t r[32];
+          tmem_ld32(taddr + c * 32, r);
+          tmem_ld_wait();
+          uint8_t* trow_ = stage + (2 * set) * OUT_TILE_BYTES + lane * 128;
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 sc = make_float4(0.f, 0.f, 0.f, 0.f), bb = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (col + j < g.N) {   // N % 4 == 0 (checked by the host)
+              sc = __ldg(reinterpret_cast<const float4*>(g.scale + col + j));
+              if (g.bias) bb = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
+            }
+            float4* cell = reinterpret_cast<float4*>(trow_ + ((((j >> 2) ^ (lane & 7))) << 4));
+            const float4 rr = *cell;
+            v[j] = __uint_as_float(r[j]) + bb.x;
+            v[j + 1] = __uint_as_float(r[j + 1]) + bb.y;
+            v[j + 2] = __uint_as_float(r[j + 2]) + bb.z;
+            v[j + 3] = __uint_as_float(r[j + 3]) + bb.w;
+            *cell = make_float4(rr.x + g.alpha * sc.x * v[j], rr.y + g.alpha * sc.y * v[j + 1],
+                                rr.z + g.alpha * sc.z * v[j + 2], rr.w + g.alpha * sc.w * v[j + 3]);
+          }
+          if (g.out2) stage_write(4, v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          stage_flush(&tmO, 2 * set, col, y);
+          if (g.out2) stage_flush(&tmO2, 4, col, y);
+          stage_commit();
+        }
       } else {
 #pragma unroll 1
         for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
@@ -475,36 +541,6 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             __syncwarp();
             stage_flush(&tmO, 0, col, y);
             stage_commit();
-          } else if (EPI == B200_EPI_RESID) {
-            // out = res + alpha * scale[col] * (acc + bias[col]); optional bf16 copy of (acc + bias)
-            float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
-            const float* rp = g.res + (long long)row * g.ldres + col;
-            if (full) {
-              float o[32];
-#pragma unroll
-              for (int j = 0; j < 32; j += 4) {
-                const float4 rr = *reinterpret_cast<const float4*>(rp + j);
-                const float4 sc = __ldg(reinterpret_cast<const float4*>(g.scale + col + j));
-                float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (g.bias) bb = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
-                v[j] += bb.x; v[j + 1] += bb.y; v[j + 2] += bb.z; v[j + 3] += bb.w;
-                o[j] = rr.x + g.alpha * sc.x * v[j];
-                o[j + 1] = rr.y + g.alpha * sc.y * v[j + 1];
-                o[j + 2] = rr.z + g.alpha * sc.z * v[j + 2];
-                o[j + 3] = rr.w + g.alpha * sc.w * v[j + 3];
-                *reinterpret_cast<float4*>(op + j) = make_float4(o[j], o[j + 1], o[j + 2], o[j + 3]);
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                if (col + j < g.N) {
-                  v[j] += g.bias ? g.bias[col + j] : 0.f;
-                  op[j] = rp[j] + g.alpha * g.scale[col + j] * v[j];
-                }
-              }
-            }
-            if (g.out2)
-              store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2, col, g.N, v);
           } else if (EPI == B200_EPI_ATOMIC_F32) {
             float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
             if (full) {
@@ -596,6 +632,20 @@ int make_tmap_bf16_out(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t 
   return r == CUDA_SUCCESS ? 0 : -2;
 }
 
+// fp32 tile map of the residual epilogue: box {32 columns, 32 rows} = 128-byte rows, 128-byte swizzle.
+int make_tmap_f32_tile(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return -1;
+  cuuint64_t gdim[2] = {cols, rows};
+  cuuint64_t gstr[1] = {ld * 4};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
 int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                       const uint32_t* box) {
   EncodeTiledFn fn = get_encode_fn();
@@ -622,7 +672,7 @@ int num_sms() {
   return n;
 }
 
-static CUtensorMap g_tm_out, g_tm_out2;  // set by b200_gemm_bf16 before launch<>() (host-side, per call)
+static CUtensorMap g_tm_out, g_tm_out2, g_tm_x;  // set by b200_gemm_bf16 before launch<>() (host-side, per call)
 
 template <int A_MN, int B_MN, int EPI>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
@@ -634,7 +684,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g
     if (e != cudaSuccess) return -3;
     configured = true;
   }
-  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g);
+  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g_tm_x, g);
   return cudaGetLastError() == cudaSuccess ? 0 : -4;
 }
 
@@ -706,6 +756,21 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   // output maps for the TMA-store epilogues
   g_tm_out = ta;
   g_tm_out2 = ta;  // placeholders when unused
+  g_tm_x = ta;
+  if (d->epi == B200_EPI_RESID) {
+    if ((d->ldo % 4) || (d->ldres % 4) || (d->N % 4) || reinterpret_cast<uintptr_t>(d->out) % 16 ||
+        reinterpret_cast<uintptr_t>(d->res) % 16 || !d->scale)
+      return -15;
+    rc = make_tmap_f32_tile(&g_tm_out, d->out, d->M, d->N, d->ldo);
+    if (rc) return rc;
+    rc = make_tmap_f32_tile(&g_tm_x, d->res, d->M, d->N, d->ldres);
+    if (rc) return rc;
+    if (d->out2) {
+      if ((d->ldo2 % 8) || reinterpret_cast<uintptr_t>(d->out2) % 16) return -15;
+      rc = make_tmap_bf16_out(&g_tm_out2, d->out2, d->M, d->N, d->ldo2);
+      if (rc) return rc;
+    }
+  }
   {
     const bool staged = d->epi == B200_EPI_BF16 || d->epi == B200_EPI_ROTARY || d->epi == B200_EPI_GEGLU ||
                         d->epi == B200_EPI_GEGLU_BWD;

@@ -74,6 +74,28 @@ def main():
     gWo = torch.zeros(D, D, device=dev)
     t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, d_o, h, gWo))
     print(f"wgrad 1024x1024  {t_:.0f} us  {2*M*D*D/t_/1e6:.0f} TF/s")
+    # the remaining per-layer shapes
+    Wo = (torch.randn(D, I, device=dev) * 0.03).bfloat16(); ao = torch.randn(M, I, device=dev).bfloat16()
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_RESID, ao, Wo, x, bias=bb, scale=sc, res=x, alpha=1.0))
+    print(f"out-proj RESID   {t_:.0f} us  {2*M*I*D/t_/1e6:.0f} TF/s")
+    dao = torch.zeros(M, I, device=dev, dtype=torch.bfloat16)
+    t_ = timeit(lambda: G.gemm(G.NN, G.EPI_BF16, d_o, Wo, dao))
+    print(f"dgrad out-proj   {t_:.0f} us  {2*M*I*D/t_/1e6:.0f} TF/s")
+    dqkv2 = torch.randn(M, 3 * I, device=dev).bfloat16()
+    t_ = timeit(lambda: G.gemm(G.NN, G.EPI_BF16, dqkv2, Wq, dh))
+    print(f"dgrad QKV        {t_:.0f} us  {2*M*3*I*D/t_/1e6:.0f} TF/s")
+    gWq = torch.zeros(3 * I, D, device=dev)
+    t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, dqkv2, h, gWq))
+    print(f"wgrad QKV        {t_:.0f} us  {2*M*3*I*D/t_/1e6:.0f} TF/s")
+    gW2 = torch.zeros(D, 4096, device=dev)
+    t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, d_o, u, gW2))
+    print(f"wgrad FF2        {t_:.0f} us  {2*M*4096*D/t_/1e6:.0f} TF/s")
+    dy = torch.randn(M, D, device=dev); dsc = torch.zeros(D, device=dev); dbi = torch.zeros(D, device=dev)
+    t_ = timeit(lambda: E.resid_bwd_prep(dy, ao, sc, dao, dsc, dbi))
+    print(f"resid_bwd_prep   {t_:.0f} us")
+    cs = torch.zeros(8192, device=dev)
+    t_ = timeit(lambda: E.colsum(dpre, cs, 1.0))
+    print(f"colsum [M,8192]  {t_:.0f} us")
 
 
     print(f"box speed (cuBLAS 8192^3): {box_speed():.0f} TF/s", flush=True)
