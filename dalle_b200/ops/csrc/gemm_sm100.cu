@@ -61,6 +61,22 @@ struct GemmDev {
   float alpha;
 };
 
+// The i-th work unit of this CTA: output tile t, k-blocks [kb0, kb1).
+struct GemmUnit { int t, kb0, kb1; };
+__device__ __forceinline__ bool gemm_unit(const GemmDev& g, int i, GemmUnit& un) {
+  const int u = blockIdx.x + i * gridDim.x;
+  if (u >= g.m_tiles * g.n_tiles * g.splits) return false;
+  const int kb_per = (g.kb_total + g.splits - 1) / g.splits;
+  // split-major order: the units of one wave share a K range, so every A / B panel of that range is pulled from
+  // HBM once and then served by L2 (tile-major order re-read the large operand once per split wave)
+  const int tiles = g.m_tiles * g.n_tiles;
+  const int split = u / tiles;
+  un.t = u - split * tiles;
+  un.kb0 = split * kb_per;
+  un.kb1 = min(un.kb0 + kb_per, g.kb_total);
+  return true;
+}
+
 // GELU pieces shared by forward and backward epilogues.  Phi(g) through Abramowitz-Stegun 7.1.26
 //   erf(x) = 1 - (a1 t + ... + a5 t^5) exp(-x^2),  t = 1 / (1 + p x),  x >= 0        (|error| <= 1.5e-7)
 // with x = |g| / sqrt(2): the exponential is exp(-g^2 / 2), i.e. the same one the density needs, so the pair costs
@@ -196,21 +212,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int units = g.m_tiles * g.n_tiles * g.splits;
-  const int kb_per = (g.kb_total + g.splits - 1) / g.splits;
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        const int split = u % g.splits;
-        const int t = u / g.splits;
-        const int n_blk = t % g.n_tiles, m_blk = t / g.n_tiles;
+      GemmUnit un;
+      for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
+        const int n_blk = un.t % g.n_tiles, m_blk = un.t / g.n_tiles;
         const int m0 = m_blk * BM, n0 = n_blk * g.tile_n_step;
-        const int kb0 = split * kb_per;
-        const int kb1 = min(kb0 + kb_per, g.kb_total);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int kb = un.kb0; kb < un.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
@@ -240,10 +251,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int u = blockIdx.x; u < units; u += gridDim.x) {
-        const int split = u % g.splits;
-        const int kb0 = split * kb_per;
-        const int kb1 = min(kb0 + kb_per, g.kb_total);
+      GemmUnit un;
+      for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
+        const int kb0 = un.kb0, kb1 = un.kb1;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
@@ -314,8 +324,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_expect_tx(&my_aux_bar[set], 2 * OUT_TILE_BYTES);
       tma_load_2d(stage + (2 * set) * OUT_TILE_BYTES, &tmX, &my_aux_bar[set], x, y);
     };
-    if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID) && blockIdx.x < units && lane == 0) {
-      const int t0 = blockIdx.x / g.splits;
+    if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID) && blockIdx.x < g.m_tiles * g.n_tiles && lane == 0) {
+      const int t0 = blockIdx.x;   // (these epilogues never split K)
       const int x0 = (t0 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
       if (x0 < g.N) {
         if (EPI == B200_EPI_RESID) res_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
@@ -324,8 +334,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int u = blockIdx.x; u < units; u += gridDim.x) {
-      const int t = u / g.splits;
+    GemmUnit un;
+    for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
+      const int t = un.t;
       const int n_blk = t % g.n_tiles, m_blk = t / g.n_tiles;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * g.tile_n_step;
@@ -382,11 +393,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             int ncol = col + 32, ny = y;
             bool have = ci + 1 < BN / 64;
             if (!have) {
-              const int u2 = u + gridDim.x;
-              have = u2 < units;
-              const int t2 = u2 / g.splits;
-              ncol = (t2 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
-              ny = (t2 / g.n_tiles) * BM + q * 32;
+              GemmUnit nx;
+              have = gemm_unit(g, ui + 1, nx);
+              ncol = (nx.t % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+              ny = (nx.t / g.n_tiles) * BM + q * 32;
             }
             if (have && ncol < g.N) {
               stage_reuse();   // the stores that read that set (two chunks ago) are done with it
@@ -446,11 +456,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             int ncol = col + 32, ny = y;
             bool have = ci + 1 < BN / 64;
             if (!have) {
-              const int u2 = u + gridDim.x;
-              have = u2 < units;
-              const int t2 = u2 / g.splits;
-              ncol = (t2 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
-              ny = (t2 / g.n_tiles) * BM + q * 32;
+              GemmUnit nx;
+              have = gemm_unit(g, ui + 1, nx);
+              ncol = (nx.t % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+              ny = (nx.t / g.n_tiles) * BM + q * 32;
             }
             if (have && ncol < g.N) {
               stage_reuse();
@@ -727,10 +736,20 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   const int tiles = g.m_tiles * g.n_tiles;
   if (splits <= 0) {
     splits = 1;
-    if (d->epi == B200_EPI_ATOMIC_F32 && tiles < 2 * num_sms()) {
-      splits = (2 * num_sms() + tiles - 1) / tiles;
-      const int max_splits = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;  // >= 4 k-blocks per unit
-      if (splits > max_splits) splits = max_splits;
+    if (d->epi == B200_EPI_ATOMIC_F32) {
+      // split K so that the (tile, split) units fill whole waves of the persistent grid: efficiency of a choice
+      // = units / (waves * #SMs); every extra split costs one more accumulating epilogue per tile
+      // (an equal-share stream-K cut of the k-block space measured 1.5x SLOWER here: CTAs at unrelated K
+      // offsets lose the L2 reuse of the A / B panels that lock-step units share)
+      const int sms = num_sms();
+      const int max_splits = g.kb_total / 32 > 0 ? (g.kb_total / 32 < 16 ? g.kb_total / 32 : 16) : 1;
+      float best = -1.f;
+      for (int sp = 1; sp <= max_splits; ++sp) {
+        const int units = tiles * sp;
+        const int waves = (units + sms - 1) / sms;
+        const float score = static_cast<float>(units) / (static_cast<float>(waves) * sms) - 0.004f * sp;
+        if (score > best) { best = score; splits = sp; }
+      }
     }
   }
   if (splits > 1 && d->epi != B200_EPI_ATOMIC_F32) return -13;
