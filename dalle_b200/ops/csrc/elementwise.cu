@@ -339,10 +339,7 @@ resid_bwd_prep_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restr
   const int rsplit = blockIdx.x / stripes, nsplit = gridDim.x / stripes;
   const float4 sc = __ldg(reinterpret_cast<const float4*>(scale + col));
   float4 as = make_float4(0.f, 0.f, 0.f, 0.f), ab = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int row = rsplit; row < M; row += nsplit) {
-    const long long off = static_cast<long long>(row) * D + col;
-    const float4 g = *reinterpret_cast<const float4*>(dy + off);
-    const uint2 u = *reinterpret_cast<const uint2*>(o + off);
+  auto one = [&](const float4& g, const uint2& u, long long off) {
     const float2 o01 = unpack_bf16x2(u.x), o23 = unpack_bf16x2(u.y);
     as.x += g.x * o01.x; as.y += g.y * o01.y; as.z += g.z * o23.x; as.w += g.w * o23.y;
     const float4 d = make_float4(g.x * sc.x, g.y * sc.y, g.z * sc.z, g.w * sc.w);
@@ -351,6 +348,23 @@ resid_bwd_prep_kernel(const float* __restrict__ dy, const __nv_bfloat16* __restr
     w.x = pack_bf16x2(d.x, d.y);
     w.y = pack_bf16x2(d.z, d.w);
     *reinterpret_cast<uint2*>(d_o + off) = w;
+  };
+  int row = rsplit;
+  for (; row + 3 * nsplit < M; row += 4 * nsplit) {   // four rows in flight per thread
+    float4 g[4];
+    uint2 u[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const long long off = static_cast<long long>(row + r * nsplit) * D + col;
+      g[r] = *reinterpret_cast<const float4*>(dy + off);
+      u[r] = *reinterpret_cast<const uint2*>(o + off);
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) one(g[r], u[r], static_cast<long long>(row + r * nsplit) * D + col);
+  }
+  for (; row < M; row += nsplit) {
+    const long long off = static_cast<long long>(row) * D + col;
+    one(*reinterpret_cast<const float4*>(dy + off), *reinterpret_cast<const uint2*>(o + off), off);
   }
   atomicAdd(dscale + col, as.x); atomicAdd(dscale + col + 1, as.y);
   atomicAdd(dscale + col + 2, as.z); atomicAdd(dscale + col + 3, as.w);
@@ -368,15 +382,29 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, long long ld, float* __r
   if (col >= N) return;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const bool full = col + 8 <= N;
-  for (int row = rsplit; row < M; row += nsplit) {
+  auto add8 = [&](const uint4& u) {
+    float2 f;
+    f = unpack_bf16x2(u.x); acc[0] += f.x; acc[1] += f.y;
+    f = unpack_bf16x2(u.y); acc[2] += f.x; acc[3] += f.y;
+    f = unpack_bf16x2(u.z); acc[4] += f.x; acc[5] += f.y;
+    f = unpack_bf16x2(u.w); acc[6] += f.x; acc[7] += f.y;
+  };
+  int row = rsplit;
+  if (full) {
+    // four rows in flight per thread (one 16-byte load per thread and iteration leaves HBM half idle)
+    for (; row + 3 * nsplit < M; row += 4 * nsplit) {
+      uint4 u[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        u[r] = *reinterpret_cast<const uint4*>(x + static_cast<long long>(row + r * nsplit) * ld + col);
+#pragma unroll
+      for (int r = 0; r < 4; ++r) add8(u[r]);
+    }
+  }
+  for (; row < M; row += nsplit) {
     const __nv_bfloat16* p = x + static_cast<long long>(row) * ld + col;
     if (full) {
-      const uint4 u = *reinterpret_cast<const uint4*>(p);
-      float2 f;
-      f = unpack_bf16x2(u.x); acc[0] += f.x; acc[1] += f.y;
-      f = unpack_bf16x2(u.y); acc[2] += f.x; acc[3] += f.y;
-      f = unpack_bf16x2(u.z); acc[4] += f.x; acc[5] += f.y;
-      f = unpack_bf16x2(u.w); acc[6] += f.x; acc[7] += f.y;
+      add8(*reinterpret_cast<const uint4*>(p));
     } else {
 #pragma unroll
       for (int j = 0; j < 8; ++j)
@@ -554,7 +582,7 @@ extern "C" int b200_resid_bwd_prep(const float* dy, const void* o, const float* 
   if (D < threads * 4) threads = D / 4;
   if (D % (threads * 4)) return -42;
   const int stripes = D / (threads * 4);
-  int nsplit = (148 * 8) / stripes;
+  int nsplit = (num_sms() * 3) / stripes;   // few, long-lived blocks: the per-thread atomics at the end are the tail
   if (nsplit > M) nsplit = M;
   if (nsplit < 1) nsplit = 1;
   resid_bwd_prep_kernel<<<stripes * nsplit, threads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
@@ -564,7 +592,7 @@ extern "C" int b200_resid_bwd_prep(const float* dy, const void* o, const float* 
 
 extern "C" int b200_colsum_bf16(const void* x, long long ld, float* out, int M, int N, float alpha, void* stream) {
   const int stripes = (N + 2047) / 2048;
-  int nsplit = (148 * 8) / stripes;
+  int nsplit = (num_sms() * 3) / stripes;   // few, long-lived blocks: the per-thread atomics at the end are the tail
   if (nsplit > M) nsplit = M;
   if (nsplit < 1) nsplit = 1;
   colsum_bf16_kernel<<<stripes * nsplit, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(

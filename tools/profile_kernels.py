@@ -22,6 +22,7 @@ dout = torch.zeros(M + 128, I, device=dev, dtype=torch.bfloat16); dout[:M] = tor
 delta = torch.zeros_like(lse); dqkv = torch.zeros(M, 3 * I, device=dev, dtype=torch.bfloat16); kv_acc = torch.zeros(M, 2 * I, device=dev)
 mean = torch.zeros(M, device=dev); rstd = torch.ones(M, device=dev); dx = torch.zeros(M, D, device=dev)
 dw = torch.zeros(D, device=dev); db = torch.zeros(D, device=dev); gW = torch.zeros(8192, D, device=dev)
+cs8k = torch.zeros(8192, device=dev)
 for _ in range(2):
     G.gemm(G.NT, G.EPI_BF16, h, W1, pre)                                        # plain NT
     G.gemm(G.NT, G.EPI_GEGLU, h, W1, u, out2=pre, bias=b1, n_half=4096)         # GEGLU + pre
@@ -32,5 +33,7 @@ for _ in range(2):
     A.attn_bwd(qkv, out, dout, lse, delta, dqkv, kv_acc, rot, cfg, "axial_row")
     E.ln_shift_fwd(x, None, sc, bb, h, mean, rstd, cfg, True)
     E.ln_shift_bwd(h, x, None, mean, rstd, sc, dx, None, dw, db, cfg, True, 0)
+    E.colsum(pre, cs8k, 1.0)
+    E.resid_bwd_prep(dx, h, sc, out, dw, db)
 torch.cuda.synchronize()
 print("ok")

@@ -20,9 +20,9 @@ def main():
         loss = model(text, image, return_loss=True)
         e1.record()
         loss.backward()
-        e2.record(); torch.cuda.synchronize()
+        e2.record(); t_enq = time.time() - t0; torch.cuda.synchronize()
         print(f"B={B} depth={depth} it={it} loss={loss.item():.4f} fwd {s.elapsed_time(e1):.1f} ms bwd {e1.elapsed_time(e2):.1f} ms "
-              f"total {s.elapsed_time(e2):.1f} ms -> {B / s.elapsed_time(e2) * 1e3:.1f} samples/s; wall {time.time()-t0:.3f}s; launches {lib.launch_count-n0}; "
+              f"total {s.elapsed_time(e2):.1f} ms -> {B / s.elapsed_time(e2) * 1e3:.1f} samples/s; wall {time.time()-t0:.3f}s (host enqueue {t_enq:.3f}s); launches {lib.launch_count-n0}; "
               f"mem {torch.cuda.max_memory_allocated()/2**30:.1f} GiB", flush=True)
     g = model.emb_weight.grad
     print("grad finite:", all(torch.isfinite(p.grad).all().item() for p in model.parameters()), "emb grad norm", g.norm().item())
