@@ -13,6 +13,7 @@
 //              256 accumulator columns
 #include "sm100_ptx.cuh"
 #include "b200_api.h"
+#include <cstdlib>
 
 #include <mutex>
 
@@ -24,19 +25,25 @@ constexpr int BK = 64;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KiB
 constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-constexpr int GEMM_THREADS = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64B-swizzled TMA-store box
 constexpr int OUT_TILES_PER_WARP = 3;
 constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
 __host__ __device__ constexpr int gemm_stages(int epi) {
   return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;
 }
+// Epilogue warps per CTA: 4 per TMEM lane quarter x column parts.  (16 warps were measured on the GEGLU backward
+// epilogue: no gain.  An ablation showed why: that kernel's time is its 1.3 GB of epilogue loads + stores, whose
+// in-flight volume is capped by the 64 KB of staging left beside the mainloop stages, not the epilogue math.)
+__host__ __device__ constexpr int gemm_epi_warps(int epi) { return 8; }
+__host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * gemm_epi_warps(epi); }  // + TMA, MMA warps
 __host__ __device__ constexpr int gemm_out_tiles(int epi) {   // staging tiles per epilogue warp
-  return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? 4 : (epi == B200_EPI_RESID ? 5 : 2));
+  return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? (gemm_epi_warps(epi) == 16 ? 2 : 4) : (epi == B200_EPI_RESID ? 5 : 2));
 }
-__host__ __device__ constexpr int gemm_out_stage_bytes(int epi) { return 8 * gemm_out_tiles(epi) * OUT_TILE_BYTES; }
+__host__ __device__ constexpr int gemm_out_stage_bytes(int epi) {
+  return gemm_epi_warps(epi) * gemm_out_tiles(epi) * OUT_TILE_BYTES;
+}
 __host__ __device__ constexpr int gemm_smem_bytes(int epi) {
-  return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 256 /*barriers*/;
+  return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 512 /*barriers*/;
 }
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 
@@ -165,7 +172,7 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* rowp, int col, int
 }
 
 template <int A_MN, int B_MN, int EPI>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2,
             const __grid_constant__ CUtensorMap tmX, const GemmDev g) {
@@ -183,7 +190,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-  uint64_t* aux_bar = bars + 2 * STAGES + 6;     // [8 warps][2 sets]: TMA loads of epilogue inputs (aux / residual)
+  uint64_t* aux_bar = bars + 2 * STAGES + 6;     // [epilogue warps][2 sets]: TMA loads of epilogue inputs (aux / residual)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -197,10 +204,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 256);
+      mbar_init(&tempty_bar[s], 32 * gemm_epi_warps(EPI));
     }
     if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID)
-      for (int s = 0; s < 16; ++s) mbar_init(&aux_bar[s], 1);
+      for (int s = 0; s < 2 * gemm_epi_warps(EPI); ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -284,7 +291,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   } else {
     // ------------------------------- epilogue warps -------------------------------------------
     const int q = warp & 3;
-    const int chalf = (warp - 2) >> 2;  // which half of the tile's columns this warp drains
+    constexpr int CPARTS = gemm_epi_warps(EPI) / 4;   // column parts of a tile (one warp per lane quarter each)
+    constexpr int NCH = BN / 32 / CPARTS;             // 32-column chunks per warp and tile
+    const int cpart = (warp - 2) >> 2;
+    constexpr int NSETS = (gemm_epi_warps(EPI) == 16) ? 1 : 2;   // staging sets of the TMA-fed epilogues
     constexpr int TILES = gemm_out_tiles(EPI);
     uint8_t* stage = smem_out + (warp - 2) * TILES * OUT_TILE_BYTES;
     // bf16 outputs leave through smem: 32 rows x 32 columns per warp and chunk, 64B-swizzled, one TMA store each
@@ -326,7 +336,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     };
     if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID) && blockIdx.x < g.m_tiles * g.n_tiles && lane == 0) {
       const int t0 = blockIdx.x;   // (these epilogues never split K)
-      const int x0 = (t0 % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+      const int x0 = (t0 % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
       if (x0 < g.N) {
         if (EPI == B200_EPI_RESID) res_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
         else aux_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
@@ -348,7 +358,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (EPI == B200_EPI_GEGLU) {
         // accumulator columns [0,128) = value half, [128,256) = gate half (same 128 output columns)
 #pragma unroll 1
-        for (int c = chalf * 2; c < chalf * 2 + 2; ++c) {
+        for (int c = cpart * (NCH / 2); c < (cpart + 1) * (NCH / 2); ++c) {
           uint32_t ra[32], rg[32];
           tmem_ld32(taddr + c * 32, ra);
           tmem_ld32(taddr + 128 + c * 32, rg);
@@ -382,64 +392,69 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       } else if (EPI == B200_EPI_GEGLU_BWD) {
         // acc = d(geglu out); aux = [value_pre | gate_pre] (bf16).  The aux tiles of a chunk arrive by TMA in the
-        // warp's staging buffers (two sets in ping-pong; per-lane row loads would cost 32 L1 wavefronts per
-        // instruction), are turned into (d value, d gate) in place and leave through TMA stores.
+        // warp's staging buffers (per-lane row loads would cost 32 L1 wavefronts per instruction), are turned into
+        // (d value, d gate) in place, 8 columns at a time, and leave through TMA stores.  With two staging sets
+        // the next chunk is fetched while this one is processed; with one set (16 epilogue warps) it is fetched as
+        // soon as this chunk's stores have read the buffers, and the other warps of the sub-partition cover it.
         const int y = m_blk * BM + q * 32;
-#pragma unroll 1
-        for (int ci = 0; ci < BN / 64; ++ci) {
-          const int c = chalf * (BN / 64) + ci;
-          const int col = n0 + c * 32;
-          {   // prefetch the next chunk (of this tile, or the first of the CTA's next tile) into the other set
-            int ncol = col + 32, ny = y;
-            bool have = ci + 1 < BN / 64;
-            if (!have) {
-              GemmUnit nx;
-              have = gemm_unit(g, ui + 1, nx);
-              ncol = (nx.t % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
-              ny = (nx.t / g.n_tiles) * BM + q * 32;
-            }
-            if (have && ncol < g.N) {
-              stage_reuse();   // the stores that read that set (two chunks ago) are done with it
-              if (lane == 0) aux_load((aux_n + 1) & 1, ncol, ny);
-            }
+        auto prefetch_next = [&](int ci, int col) {
+          int ncol = col + 32, ny = y;
+          bool have = ci + 1 < NCH;
+          if (!have) {
+            GemmUnit nx;
+            have = gemm_unit(g, ui + 1, nx);
+            ncol = (nx.t % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
+            ny = (nx.t / g.n_tiles) * BM + q * 32;
           }
+          if (have && ncol < g.N) {
+            stage_reuse();   // the stores that last read that set are done with it
+            if (lane == 0) aux_load(aux_n % NSETS, ncol, ny);   // (aux_n already counts the current chunk)
+          }
+        };
+#pragma unroll 1
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c = cpart * NCH + ci;
+          const int col = n0 + c * 32;
           if (col >= g.N) continue;  // warp-uniform (never prefetched either)
-          const int set = aux_n & 1;
-          mbar_wait(&my_aux_bar[set], (aux_n >> 1) & 1);
+          const int set = aux_n % NSETS;
+          const uint32_t par = (aux_n / NSETS) & 1;
           ++aux_n;
+          if (NSETS == 2) prefetch_next(ci, col);
+          mbar_wait(&my_aux_bar[set], par);
           uint32_t r[32];
           tmem_ld32(taddr + c * 32, r);
           tmem_ld_wait();
-          const uint8_t* ta_ = stage + (2 * set) * OUT_TILE_BYTES + lane * 64;
-          const uint8_t* tg_ = ta_ + OUT_TILE_BYTES;
+          uint8_t* ta_ = stage + (2 * set) * OUT_TILE_BYTES + lane * 64;
+          uint8_t* tg_ = ta_ + OUT_TILE_BYTES;
           const int sw = (lane >> 1) & 3;
-          float da[32], dg[32];
 #pragma unroll
           for (int p8 = 0; p8 < 4; ++p8) {
-            const uint4 ua = *reinterpret_cast<const uint4*>(ta_ + ((p8 ^ sw) << 4));
-            const uint4 ug = *reinterpret_cast<const uint4*>(tg_ + ((p8 ^ sw) << 4));
+            uint4* pa = reinterpret_cast<uint4*>(ta_ + ((p8 ^ sw) << 4));
+            uint4* pg = reinterpret_cast<uint4*>(tg_ + ((p8 ^ sw) << 4));
+            const uint4 ua = *pa, ug = *pg;
             const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wg[4] = {ug.x, ug.y, ug.z, ug.w};
+            uint32_t oa[4], og[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const int j = p8 * 8 + e * 2;
               const float2 a2 = unpack_bf16x2(wa[e]), g2 = unpack_bf16x2(wg[e]);
-              const float2 v2 = row_ok ? make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]))
-                                       : make_float2(0.f, 0.f);
+              // (rows past M: zero-filled A rows give a zero accumulator, and the TMA store clips them)
+              const float2 v2 = make_float2(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
               const GeluParts2 gp = gelu_parts2(g2);
               const float2 x = __fmul2_rn(__fmul2_rn(v2, g2), gp.cdf);
               const float2 y2 = __fmul2_rn(__fmul2_rn(v2, a2), __ffma2_rn(g2, gp.pdf, gp.cdf));
-              da[j] = x.x; da[j + 1] = x.y;
-              dg[j] = y2.x; dg[j + 1] = y2.y;
+              oa[e] = pack_bf16x2(x.x, x.y);
+              og[e] = pack_bf16x2(y2.x, y2.y);
             }
+            *pa = make_uint4(oa[0], oa[1], oa[2], oa[3]);
+            *pg = make_uint4(og[0], og[1], og[2], og[3]);
           }
-          __syncwarp();
-          stage_write(2 * set, da);
-          stage_write(2 * set + 1, dg);
           fence_proxy_async_smem();
           __syncwarp();
           stage_flush(&tmO, 2 * set, col, y);
           stage_flush(&tmO, 2 * set + 1, g.n_half + col, y);
           stage_commit();
+          if (NSETS == 1) prefetch_next(ci, col);
         }
       } else if (EPI == B200_EPI_RESID) {
         // out = res + alpha * scale[col] * (acc + bias[col]); optional bf16 copy of (acc + bias).
@@ -449,16 +464,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         // serialisation when `res` is `out` (the in-place residual stream).
         const int y = m_blk * BM + q * 32;
 #pragma unroll 1
-        for (int ci = 0; ci < BN / 64; ++ci) {
-          const int c = chalf * (BN / 64) + ci;
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c = cpart * NCH + ci;
           const int col = n0 + c * 32;
           {
             int ncol = col + 32, ny = y;
-            bool have = ci + 1 < BN / 64;
+            bool have = ci + 1 < NCH;
             if (!have) {
               GemmUnit nx;
               have = gemm_unit(g, ui + 1, nx);
-              ncol = (nx.t % g.n_tiles) * g.tile_n_step + chalf * (BN / 64) * 32;
+              ncol = (nx.t % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
               ny = (nx.t / g.n_tiles) * BM + q * 32;
             }
             if (have && ncol < g.N) {
@@ -500,7 +515,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       } else {
 #pragma unroll 1
-        for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
+        for (int c = cpart * NCH; c < (cpart + 1) * NCH; ++c) {
           const int col = n0 + c * 32;
           if (col >= g.N) break;  // warp-uniform
           uint32_t r[32];
@@ -693,7 +708,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g
     if (e != cudaSuccess) return -3;
     configured = true;
   }
-  kern<<<grid, GEMM_THREADS, smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g_tm_x, g);
+  kern<<<grid, gemm_threads(EPI), smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g_tm_x, g);
   return cudaGetLastError() == cudaSuccess ? 0 : -4;
 }
 

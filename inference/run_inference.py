@@ -20,8 +20,6 @@ from dalle_b200.config import get_config  # noqa: E402
 from dalle_b200.models.dalle import DALLE, ModelWrapper  # noqa: E402
 from dalle_b200.training.tokenizer import load_tokenizer  # noqa: E402
 
-torch.set_grad_enabled(False)
-
 
 def make_model(preset: str = "ttt", tokenizer_path: str = "t5-small"):
     tokenizer = load_tokenizer(tokenizer_path)
@@ -48,6 +46,13 @@ def generate(query, *, tokenizer, model, batch_size, n_iters, temperature, top_k
 
 
 def main(argv=None):
+    # (the reference script disables autograd at import time; doing it here keeps importing this module from
+    # tests or other tools free of that process-wide side effect)
+    with torch.no_grad():
+        return _main(argv)
+
+
+def _main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--queries", type=str, help="List of queries (*.txt, newline-separated)")
     ap.add_argument("--temperature", type=float, default=1.0, help="Sampling temperature")
