@@ -8,6 +8,10 @@ over preallocated buffers:
 * residual streams X1, X2 live in fp32 and are updated IN PLACE by the GEMM epilogues
   (``y = x + scale * (acc + bias)`` forward, ``x = y - scale * (acc + bias)`` when reconstructing), so activation
   memory is O(1) in depth exactly like the RevNet formulation;
+* the reference needs that recomputation to fit 16 GB cards; a B200 has 180 GB, so the first ``store_layers``
+  layers (as many as fit, all 64 at the benchmark batch) KEEP their activations instead - their backward runs no
+  forward kernels at all (about a quarter of a training step) and reads the saved tensors; the remaining layers, if
+  any, use the reversible path.  Both produce the same gradients (tests/test_executor.py runs every split);
 * GEMM operands are bf16; weights have bf16 shadows refreshed when the fp32 masters change;
 * parameter gradients are accumulated straight into the fp32 ``.grad`` buffers (the collaborative optimizer's
   ``reuse_grad_buffers=True`` contract, reference arguments.py:75-78) - wgrad GEMMs ``red.add`` into them;
@@ -20,6 +24,7 @@ hand-written backward below is verified against plain autograd on CPU (tests/tes
 from __future__ import annotations
 
 import math
+import os
 from typing import Dict, Optional
 
 import torch
@@ -33,12 +38,19 @@ class _Buffers:
     pass
 
 
+class _Saved:
+    """Activations one layer keeps for its backward when it is not recomputed."""
+
+
 class Engine:
     LOGIT_CHUNK_BYTES = 384 << 20
+    STORE_RESERVE_BYTES = 20 << 30   # HBM left alone when sizing the stored-activation pool (optimizer, NCCL, ...)
 
-    def __init__(self, model):
+    def __init__(self, model, store_layers: Optional[int] = None):
         self.model = model
         self.cfg = model.cfg
+        env = os.environ.get("DALLE_B200_STORE_LAYERS")
+        self.store_layers = int(env) if env not in (None, "") else store_layers   # None: as many as fit
         self._bufs: Dict[tuple, _Buffers] = {}
         self._shadow: Dict[int, torch.Tensor] = {}
         self._shadow_version: Dict[int, int] = {}
@@ -136,8 +148,58 @@ class Engine:
             b.delta = z(B, cfg.heads, cfg.seq_len, dtype=torch.float32)
             b.kv_acc = z(M, 2 * I, dtype=torch.float32)
             b.dhf = z(M, D)
+            self._alloc_saved(b, B, device)
+        else:
+            b.saved = []
         self._bufs[key] = b
         return b
+
+    def saved_bytes_per_layer(self, B: int, device) -> int:
+        cfg = self.cfg
+        M, D, I = B * cfg.seq_len, cfg.dim, cfg.inner_dim
+        hid = D * cfg.ff_mult
+        e = 2 if device.type == "cuda" else 4
+        return (2 * M * D * 4                      # the two fp32 streams after the layer's blocks
+                + e * (2 * M * D + (M + 128) * 3 * I + M * I + 2 * M * D + 2 * M * hid + M * hid)  # h, qkv, ao, o, pre, u
+                + 4 * (4 * M + B * cfg.heads * cfg.seq_len))
+
+    def _alloc_saved(self, b: _Buffers, B: int, device):
+        """Per-layer activation pool of the layers whose backward does not recompute (see the module docstring)."""
+        cfg = self.cfg
+        n = self.store_layers
+        if n is None:
+            if device.type == "cuda":
+                free, _ = torch.cuda.mem_get_info(device)
+                n = max(0, (free - self.STORE_RESERVE_BYTES) // self.saved_bytes_per_layer(B, device))
+            else:
+                n = cfg.depth
+        n = int(min(cfg.depth, max(0, n)))
+        M, D, I = B * cfg.seq_len, cfg.dim, cfg.inner_dim
+        hid = D * cfg.ff_mult
+        ad = self.act_dtype(device)
+
+        def e(*shape, dtype=ad):
+            return torch.empty(*shape, device=device, dtype=dtype)
+
+        b.saved = []
+        for i in range(n):
+            s = _Saved()
+            last = i == n - 1
+            # stream values after the attention block (x1) and after the feed-forward block (x2); the last stored
+            # layer writes the shared work streams, which the reversible layers behind it reconstruct in place
+            s.x1 = b.x1 if last else e(M, D, dtype=torch.float32)
+            s.x2 = b.x2 if last else e(M, D, dtype=torch.float32)
+            s.h_f, s.h_g = e(M, D), e(M, D)
+            s.qkv = e(M + 128, 3 * I)
+            s.qkv[M:].zero_()
+            s.ao, s.o_f, s.o_g = e(M, I), e(M, D), e(M, D)
+            s.lse = e(B, cfg.heads, cfg.seq_len, dtype=torch.float32)
+            s.pre, s.u = e(M, 2 * hid), e(M, hid)
+            s.mean_f, s.rstd_f = e(M, dtype=torch.float32), e(M, dtype=torch.float32)
+            s.mean_g, s.rstd_g = e(M, dtype=torch.float32), e(M, dtype=torch.float32)
+            b.saved.append(s)
+        if n > 0:   # the embedding output must survive layer 0 (its x2 half is an LN input of the backward)
+            b.e1, b.e2 = e(M, D, dtype=torch.float32), e(M, D, dtype=torch.float32)
 
     # ------------------------------------------------------------------------------------------
     # token ids
@@ -157,35 +219,53 @@ class Engine:
     # ------------------------------------------------------------------------------------------
     # layer pieces
     # ------------------------------------------------------------------------------------------
-    def _f_forward(self, i, b, src, dst, alpha, save_o=False):
-        """dst <- dst + alpha * scale_f[i] * attn(shift(LN(src)))   (in place on dst)"""
+    def _f_forward(self, i, b, src, dst, alpha, save_o=False, keep: Optional[_Saved] = None, res=None):
+        """dst <- res + alpha * scale_f[i] * attn(shift(LN(src)))   (res defaults to dst: in place).
+        With ``keep`` the intermediates land in that layer's saved set instead of the shared work buffers."""
         m, cfg = self.model, self.cfg
         a = m.attn_index[i]
         M = src.shape[0]
-        E.ln_shift_fwd(src, None, m.norm_f_w[i], m.norm_f_b[i], b.h, b.mean, b.rstd, cfg, True)
-        G.gemm(G.NT, G.EPI_ROTARY, b.h, self.w(m.attn_qkv_w[a]), b.qkv[:M], rot=m.rotary_pairs, seq_len=cfg.seq_len,
+        h, qkv, ao, lse = (keep.h_f, keep.qkv, keep.ao, keep.lse) if keep else (b.h, b.qkv, b.ao, b.lse)
+        mean, rstd = (keep.mean_f, keep.rstd_f) if keep else (b.mean, b.rstd)
+        o = keep.o_f if keep else (b.o if save_o else None)
+        E.ln_shift_fwd(src, None, m.norm_f_w[i], m.norm_f_b[i], h, mean, rstd, cfg, True)
+        G.gemm(G.NT, G.EPI_ROTARY, h, self.w(m.attn_qkv_w[a]), qkv[:M], rot=m.rotary_pairs, seq_len=cfg.seq_len,
                q_cols=cfg.inner_dim, q_scale=cfg.dim_head ** -0.5)
-        A.attn_fwd(b.qkv, b.ao, b.lse, cfg, cfg.attn_types[i])
-        G.gemm(G.NT, G.EPI_RESID, b.ao, self.w(m.attn_out_w[a]), dst, out2=b.o if save_o else None,
-               bias=m.attn_out_b[a], scale=m.scale_f[i].view(-1), res=dst, alpha=alpha)
+        A.attn_fwd(qkv, ao, lse, cfg, cfg.attn_types[i])
+        G.gemm(G.NT, G.EPI_RESID, ao, self.w(m.attn_out_w[a]), dst, out2=o, bias=m.attn_out_b[a],
+               scale=m.scale_f[i].view(-1), res=dst if res is None else res, alpha=alpha)
 
-    def _g_forward(self, i, b, src, dst, alpha, save=False):
-        """dst <- dst + alpha * scale_g[i] * ff(shift(LN(src)))"""
+    def _g_forward(self, i, b, src, dst, alpha, save=False, keep: Optional[_Saved] = None, res=None):
+        """dst <- res + alpha * scale_g[i] * ff(shift(LN(src)))"""
         m, cfg = self.model, self.cfg
         f = m.ff_index[i]
         hid = cfg.dim * cfg.ff_mult
-        E.ln_shift_fwd(src, None, m.norm_g_w[i], m.norm_g_b[i], b.h, b.mean, b.rstd, cfg, True)
-        G.gemm(G.NT, G.EPI_GEGLU, b.h, self.w(m.ff_w1[f]), b.u, out2=b.pre if save else None, bias=m.ff_b1[f],
-               n_half=hid)
-        G.gemm(G.NT, G.EPI_RESID, b.u, self.w(m.ff_w2[f]), dst, out2=b.o if save else None, bias=m.ff_b2[f],
-               scale=m.scale_g[i].view(-1), res=dst, alpha=alpha)
+        h, u = (keep.h_g, keep.u) if keep else (b.h, b.u)
+        mean, rstd = (keep.mean_g, keep.rstd_g) if keep else (b.mean, b.rstd)
+        pre = keep.pre if keep else (b.pre if save else None)
+        o = keep.o_g if keep else (b.o if save else None)
+        E.ln_shift_fwd(src, None, m.norm_g_w[i], m.norm_g_b[i], h, mean, rstd, cfg, True)
+        G.gemm(G.NT, G.EPI_GEGLU, h, self.w(m.ff_w1[f]), u, out2=pre, bias=m.ff_b1[f], n_half=hid)
+        G.gemm(G.NT, G.EPI_RESID, u, self.w(m.ff_w2[f]), dst, out2=o, bias=m.ff_b2[f],
+               scale=m.scale_g[i].view(-1), res=dst if res is None else res, alpha=alpha)
 
     def run_stack(self, ids: torch.Tensor, b: _Buffers):
         cfg = self.cfg
-        E.embed_fwd(ids.view(-1), self.model.emb_weight.detach(), b.x1, b.x2)
+        saved = b.saved
+        if not saved:
+            E.embed_fwd(ids.view(-1), self.model.emb_weight.detach(), b.x1, b.x2)
+        else:
+            E.embed_fwd(ids.view(-1), self.model.emb_weight.detach(), b.e1, b.e2)
+        c1, c2 = (b.e1, b.e2) if saved else (b.x1, b.x2)   # current stream values
         for i in range(cfg.depth):
-            self._f_forward(i, b, b.x2, b.x1, 1.0)
-            self._g_forward(i, b, b.x1, b.x2, 1.0)
+            if i < len(saved):
+                s = saved[i]
+                self._f_forward(i, b, c2, s.x1, 1.0, keep=s, res=c1)
+                self._g_forward(i, b, s.x1, s.x2, 1.0, keep=s, res=c2)
+                c1, c2 = s.x1, s.x2          # (the last stored layer's are b.x1 / b.x2)
+            else:
+                self._f_forward(i, b, b.x2, b.x1, 1.0)
+                self._g_forward(i, b, b.x1, b.x2, 1.0)
 
     # ------------------------------------------------------------------------------------------
     # head: final norm + segment logits + weighted CE
@@ -234,15 +314,19 @@ class Engine:
         m, cfg = self.model, self.cfg
         f = m.ff_index[i]
         hid = cfg.dim * cfg.ff_mult
-        self._g_forward(i, b, b.x1, b.x2, -1.0, save=True)          # recompute + reconstruct x2 in place
+        s = b.saved[i] if i < len(b.saved) else None
+        if s is None:
+            self._g_forward(i, b, b.x1, b.x2, -1.0, save=True)          # recompute + reconstruct x2 in place
+        o, u, pre, h = (s.o_g, s.u, s.pre, s.h_g) if s else (b.o, b.u, b.pre, b.h)
+        x1, mean, rstd = (s.x1, s.mean_g, s.rstd_g) if s else (b.x1, b.mean, b.rstd)
         sg = m.scale_g[i]
-        E.resid_bwd_prep(b.dx2, b.o, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
-        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, b.u, self.grad_of(m.ff_w2[f]))
-        G.gemm(G.NN, G.EPI_GEGLU_BWD, b.d_o, self.w(m.ff_w2[f]), b.dpre, aux=b.pre, n_half=hid)
+        E.resid_bwd_prep(b.dx2, o, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, u, self.grad_of(m.ff_w2[f]))
+        G.gemm(G.NN, G.EPI_GEGLU_BWD, b.d_o, self.w(m.ff_w2[f]), b.dpre, aux=pre, n_half=hid)
         E.colsum(b.dpre, self.grad_of(m.ff_b1[f]))
-        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dpre, b.h, self.grad_of(m.ff_w1[f]))
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dpre, h, self.grad_of(m.ff_w1[f]))
         G.gemm(G.NN, G.EPI_BF16, b.dpre, self.w(m.ff_w1[f]), b.dh)
-        E.ln_shift_bwd(b.dh, b.x1, None, b.mean, b.rstd, m.norm_g_w[i], b.dx1, None, self.grad_of(m.norm_g_w[i]),
+        E.ln_shift_bwd(b.dh, x1, None, mean, rstd, m.norm_g_w[i], b.dx1, None, self.grad_of(m.norm_g_w[i]),
                        self.grad_of(m.norm_g_b[i]), cfg, True, 0)
 
     def _f_backward(self, i, b):
@@ -250,15 +334,21 @@ class Engine:
         m, cfg = self.model, self.cfg
         a = m.attn_index[i]
         M = b.x1.shape[0]
-        self._f_forward(i, b, b.x2, b.x1, -1.0, save_o=True)
+        s = b.saved[i] if i < len(b.saved) else None
+        if s is None:
+            self._f_forward(i, b, b.x2, b.x1, -1.0, save_o=True)
+        o, ao, qkv, lse, h = (s.o_f, s.ao, s.qkv, s.lse, s.h_f) if s else (b.o, b.ao, b.qkv, b.lse, b.h)
+        mean, rstd = (s.mean_f, s.rstd_f) if s else (b.mean, b.rstd)
+        # LN input of the attention block: the x2 stream entering the layer
+        x2 = b.x2 if s is None else (b.saved[i - 1].x2 if i > 0 else b.e2)
         sf = m.scale_f[i]
-        E.resid_bwd_prep(b.dx1, b.o, sf.view(-1), b.d_o, self.grad_of(sf).view(-1), self.grad_of(m.attn_out_b[a]))
-        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, b.ao, self.grad_of(m.attn_out_w[a]))
+        E.resid_bwd_prep(b.dx1, o, sf.view(-1), b.d_o, self.grad_of(sf).view(-1), self.grad_of(m.attn_out_b[a]))
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, ao, self.grad_of(m.attn_out_w[a]))
         G.gemm(G.NN, G.EPI_BF16, b.d_o, self.w(m.attn_out_w[a]), b.dao[:M])
-        A.attn_bwd(b.qkv, b.ao, b.dao, b.lse, b.delta, b.dqkv, b.kv_acc, m.rotary_pairs, cfg, cfg.attn_types[i])
-        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dqkv, b.h, self.grad_of(m.attn_qkv_w[a]))
+        A.attn_bwd(qkv, ao, b.dao, lse, b.delta, b.dqkv, b.kv_acc, m.rotary_pairs, cfg, cfg.attn_types[i])
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dqkv, h, self.grad_of(m.attn_qkv_w[a]))
         G.gemm(G.NN, G.EPI_BF16, b.dqkv, self.w(m.attn_qkv_w[a]), b.dh)
-        E.ln_shift_bwd(b.dh, b.x2, None, b.mean, b.rstd, m.norm_f_w[i], b.dx2, None, self.grad_of(m.norm_f_w[i]),
+        E.ln_shift_bwd(b.dh, x2, None, mean, rstd, m.norm_f_w[i], b.dx2, None, self.grad_of(m.norm_f_w[i]),
                        self.grad_of(m.norm_f_b[i]), cfg, True, 0)
 
     # ------------------------------------------------------------------------------------------

@@ -25,10 +25,14 @@ def _boost(model, v=0.25):
             p.uniform_(-0.2, 0.2)
 
 
+# store_layers: how many layers keep their activations instead of being recomputed by the reversible backward
+# (None = all that fit; 0 = the reference's pure reversible scheme; 1 = one stored layer in front of reversible ones)
+@pytest.mark.parametrize("store_layers", [None, 0, 1])
 @pytest.mark.parametrize("cfg_fn", [tiny_config, small_config])
-def test_executor_matches_autograd(cfg_fn):
+def test_executor_matches_autograd(cfg_fn, store_layers):
     cfg = cfg_fn()
     model = DALLE(cfg, seed=0)
+    model.engine.store_layers = store_layers
     _boost(model)
     text, image = _batch(cfg)
     ref_loss = model.forward_reference(text, image, return_loss=True)

@@ -24,12 +24,14 @@ def _boost(model, v=0.25):
             p.uniform_(0.7, 1.3)
 
 
+@pytest.mark.parametrize("store_layers", [None, 0, 1])   # stored activations / reversible recompute / mixed
 @pytest.mark.parametrize("cfg_fn", [tiny_config, small_config])
-def test_gpu_executor_matches_fp32_oracle(cfg_fn):
+def test_gpu_executor_matches_fp32_oracle(cfg_fn, store_layers):
     cfg = cfg_fn()
     ref = DALLE(cfg, seed=0)
     _boost(ref)
     model = DALLE(cfg, seed=0)
+    model.engine.store_layers = store_layers
     model.load_state_dict(ref.state_dict())
     model.cuda()
     text, image = _batch(cfg)
