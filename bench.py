@@ -107,6 +107,17 @@ def reference_arm(args):
     return 0
 
 
+def activation_policy(trainer, B, cfg):
+    """How many layers kept their activations for the backward (the rest are recomputed, reversible-style)."""
+    try:
+        eng = trainer.model.engine
+        bufs = eng._bufs.get((B, str(trainer.device), True))
+        n = len(bufs.saved) if bufs is not None else 0
+        return f"stored for {n}/{cfg.depth} layers, reversible recompute for the rest (same gradients)"
+    except Exception:  # reference arm / eager baseline
+        return "n/a"
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -216,6 +227,7 @@ def main():
                        "global_batch": B * world, "micro_batch_per_gpu": B, "seq_len": cfg.seq_len,
                        "parallelism": f"dp{world}", "optimizer": "LAMB-8bit, one update per step",
                        "averaging": getattr(trainer, "averaging", "n/a"),
+                       "activations": activation_policy(trainer, B, cfg),
                        "l2": "per-step working set (>5 GB activations/weights) exceeds the 126 MB L2; no flush"},
             "exposed_averaging_ms_per_step": exposed_ms,
             "exposed_averaging_share": (exposed_ms / (ms_total / K)) if exposed_ms else None,
