@@ -309,8 +309,24 @@ class Engine:
     # ------------------------------------------------------------------------------------------
     # backward of one layer (reconstructs the inputs in place)
     # ------------------------------------------------------------------------------------------
-    def _g_backward(self, i, b):
-        """y2 = x2 + sg*ff(..y1..):  X2 <- x2 ; dX1 += d ff / d y1 ; param grads."""
+    def _next_prep_f(self, i, b):
+        """Arguments that fold the attention block's residual prologue (layer i) into the LN backward before it."""
+        if i >= len(b.saved):
+            return None   # recomputed layer: its `o` does not exist yet
+        m = self.model
+        sf, a = m.scale_f[i], m.attn_index[i]
+        return (b.saved[i].o_f, sf.view(-1), b.d_o, self.grad_of(sf).view(-1), self.grad_of(m.attn_out_b[a]))
+
+    def _next_prep_g(self, i, b):
+        if i < 0 or i >= len(b.saved):
+            return None
+        m = self.model
+        sg, f = m.scale_g[i], m.ff_index[i]
+        return (b.saved[i].o_g, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
+
+    def _g_backward(self, i, b, prepped=False):
+        """y2 = x2 + sg*ff(..y1..):  X2 <- x2 ; dX1 += d ff / d y1 ; param grads.  Returns True when the attention
+        block's prologue (d_o, dscale, dbias) has already been produced by the fused LN backward."""
         m, cfg = self.model, self.cfg
         f = m.ff_index[i]
         hid = cfg.dim * cfg.ff_mult
@@ -320,17 +336,21 @@ class Engine:
         o, u, pre, h = (s.o_g, s.u, s.pre, s.h_g) if s else (b.o, b.u, b.pre, b.h)
         x1, mean, rstd = (s.x1, s.mean_g, s.rstd_g) if s else (b.x1, b.mean, b.rstd)
         sg = m.scale_g[i]
-        E.resid_bwd_prep(b.dx2, o, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
+        if not prepped:
+            E.resid_bwd_prep(b.dx2, o, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
         G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, u, self.grad_of(m.ff_w2[f]))
         G.gemm(G.NN, G.EPI_GEGLU_BWD, b.d_o, self.w(m.ff_w2[f]), b.dpre, aux=pre, n_half=hid)
         E.colsum(b.dpre, self.grad_of(m.ff_b1[f]))
         G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dpre, h, self.grad_of(m.ff_w1[f]))
         G.gemm(G.NN, G.EPI_BF16, b.dpre, self.w(m.ff_w1[f]), b.dh)
+        nxt = self._next_prep_f(i, b)
         E.ln_shift_bwd(b.dh, x1, None, mean, rstd, m.norm_g_w[i], b.dx1, None, self.grad_of(m.norm_g_w[i]),
-                       self.grad_of(m.norm_g_b[i]), cfg, True, 0)
+                       self.grad_of(m.norm_g_b[i]), cfg, True, 0, next_prep=nxt)
+        return nxt is not None
 
-    def _f_backward(self, i, b):
-        """y1 = x1 + sf*attn(..x2..):  X1 <- x1 ; dX2 += d attn / d x2 ; param grads."""
+    def _f_backward(self, i, b, prepped=False):
+        """y1 = x1 + sf*attn(..x2..):  X1 <- x1 ; dX2 += d attn / d x2 ; param grads.  Returns True when the previous
+        layer's feed-forward prologue has already been produced by the fused LN backward."""
         m, cfg = self.model, self.cfg
         a = m.attn_index[i]
         M = b.x1.shape[0]
@@ -342,14 +362,17 @@ class Engine:
         # LN input of the attention block: the x2 stream entering the layer
         x2 = b.x2 if s is None else (b.saved[i - 1].x2 if i > 0 else b.e2)
         sf = m.scale_f[i]
-        E.resid_bwd_prep(b.dx1, o, sf.view(-1), b.d_o, self.grad_of(sf).view(-1), self.grad_of(m.attn_out_b[a]))
+        if not prepped:
+            E.resid_bwd_prep(b.dx1, o, sf.view(-1), b.d_o, self.grad_of(sf).view(-1), self.grad_of(m.attn_out_b[a]))
         G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, ao, self.grad_of(m.attn_out_w[a]))
         G.gemm(G.NN, G.EPI_BF16, b.d_o, self.w(m.attn_out_w[a]), b.dao[:M])
         A.attn_bwd(qkv, ao, b.dao, lse, b.delta, b.dqkv, b.kv_acc, m.rotary_pairs, cfg, cfg.attn_types[i])
         G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dqkv, h, self.grad_of(m.attn_qkv_w[a]))
         G.gemm(G.NN, G.EPI_BF16, b.dqkv, self.w(m.attn_qkv_w[a]), b.dh)
+        nxt = self._next_prep_g(i - 1, b)
         E.ln_shift_bwd(b.dh, x2, None, mean, rstd, m.norm_f_w[i], b.dx2, None, self.grad_of(m.norm_f_w[i]),
-                       self.grad_of(m.norm_f_b[i]), cfg, True, 0)
+                       self.grad_of(m.norm_f_b[i]), cfg, True, 0, next_prep=nxt)
+        return nxt is not None
 
     # ------------------------------------------------------------------------------------------
     # public entry points
@@ -383,9 +406,10 @@ class Engine:
         E.ln_shift_bwd(b.dhf, b.x1, b.x2, b.fmean, b.frstd, m.final_norm_w, b.dx1, b.dx2,
                        self.grad_of(m.final_norm_w), self.grad_of(m.final_norm_b), cfg, False, 1,
                        row_split=cfg.text_seq_len)
+        prepped = False
         for i in reversed(range(cfg.depth)):
-            self._g_backward(i, b)
-            self._f_backward(i, b)
+            prepped = self._g_backward(i, b, prepped)
+            prepped = self._f_backward(i, b, prepped)
         E.embed_bwd(ids.view(-1), b.dx1, b.dx2, self.grad_of(m.emb_weight))
 
     @torch.no_grad()

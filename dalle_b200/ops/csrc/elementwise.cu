@@ -208,12 +208,24 @@ ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, c
 // Persistent blocks of 4 row groups x 128 threads: a group walks rows with a grid stride and a thread owns the same
 // <= 8 columns on every row, so dw / db accumulate in registers and leave through one shared-memory reduction +
 // global atomics per block.  All loads of a row (dh, x, the old dx) are issued before the first use.
-constexpr int LNB_GROUPS = 4;
-__global__ void __launch_bounds__(128 * LNB_GROUPS, 2)
+// Optional tail of the mode-0 kernel: the stream gradient it has just completed (y = dx_out) is exactly what the
+// next block of the backward walk starts from, so its LayerScale/residual prologue is done on the values in
+// registers:  d_o = bf16(y * scale),  dscale += colsum(y * o),  dbias += colsum(y * scale)   (resid_bwd_prep)
+struct LnBwdNext {
+  const __nv_bfloat16* o;   // that block's output before LayerScale (kept from the forward); nullptr: no tail
+  const float* scale;
+  __nv_bfloat16* d_o;
+  float* dscale;
+  float* dbias;
+};
+// Two row groups of 128 threads per block; three blocks per SM (<= 85 registers) without the tail, two (<= 128
+// registers) with it - sized so that neither variant spills.
+template <int LNB_GROUPS, bool TAIL>
+__global__ void __launch_bounds__(128 * LNB_GROUPS, TAIL ? 2 : 3)
 ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
                     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
                     float* __restrict__ dx_out, float* __restrict__ dx2_out, float* __restrict__ dw,
-                    float* __restrict__ db, int M, int D, ShiftGeom sg, int mode) {
+                    float* __restrict__ db, int M, int D, ShiftGeom sg, int mode, LnBwdNext nx) {
   __shared__ float sred[LNB_GROUPS][2][4][2];   // [group][parity][warp][s1, s2]
   __shared__ float s_acc[LNB_GROUPS - 1][2][128 * MAXV];
   const int grp = threadIdx.x >> 7;            // row group of the block
@@ -231,6 +243,13 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
   }
   float4 aw[2], ab[2];
   aw[0] = aw[1] = ab[0] = ab[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 nsc[2], as2[2], ab2[2];   // tail: next block's LayerScale, its dscale / dbias partial sums
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    as2[k] = ab2[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    nsc[k] = (TAIL && act[k]) ? __ldg(reinterpret_cast<const float4*>(nx.scale + colk[k]))
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const int groups_total = gridDim.x * LNB_GROUPS;
   const int rows_per = (M + groups_total - 1) / groups_total;   // every row group owns a contiguous range of rows
   const int row_begin = min(M, (blockIdx.x * LNB_GROUPS + grp) * rows_per), row_end = min(M, row_begin + rows_per);
@@ -243,11 +262,11 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
     const long long r_q0 = rt.dst[0] >= 0 ? static_cast<long long>(permuted_row32(sg, rw.bidx, rt.dst[0])) * D : -1;
     const long long r_q1 = rt.dst[1] >= 0 ? static_cast<long long>(permuted_row32(sg, rw.bidx, rt.dst[1])) * D : -1;
     const float mu = mean[row], rs = rstd[row];
-    uint2 u[2];
+    uint2 u[2], uo[2];
     float4 v[2], v2[2], old[2];
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-      u[k] = make_uint2(0u, 0u);
+      u[k] = uo[k] = make_uint2(0u, 0u);
       v[k] = v2[k] = old[k] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (act[k]) {
         const int col = colk[k];
@@ -256,6 +275,7 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
         v[k] = *reinterpret_cast<const float4*>(x + static_cast<long long>(row) * D + col);
         if (x2) v2[k] = *reinterpret_cast<const float4*>(x2 + static_cast<long long>(row) * D + col);
         if (mode == 0) old[k] = *reinterpret_cast<const float4*>(dx_out + static_cast<long long>(row) * D + col);
+        if (TAIL) uo[k] = *reinterpret_cast<const uint2*>(nx.o + static_cast<long long>(row) * D + col);
       }
     }
     float4 dn[2], xh[2];
@@ -291,7 +311,18 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
         d.w = rs * (dn[k].w - s1 - xh[k].w * s2);
         float4* p = reinterpret_cast<float4*>(dx_out + static_cast<long long>(row) * D + colk[k]);
         if (mode == 0) {
-          *p = make_float4(old[k].x + d.x, old[k].y + d.y, old[k].z + d.z, old[k].w + d.w);
+          const float4 y = make_float4(old[k].x + d.x, old[k].y + d.y, old[k].z + d.z, old[k].w + d.w);
+          *p = y;
+          if (TAIL) {
+            const float2 o01 = unpack_bf16x2(uo[k].x), o23 = unpack_bf16x2(uo[k].y);
+            const float4 ys = make_float4(y.x * nsc[k].x, y.y * nsc[k].y, y.z * nsc[k].z, y.w * nsc[k].w);
+            as2[k].x += y.x * o01.x; as2[k].y += y.y * o01.y; as2[k].z += y.z * o23.x; as2[k].w += y.w * o23.y;
+            ab2[k].x += ys.x; ab2[k].y += ys.y; ab2[k].z += ys.z; ab2[k].w += ys.w;
+            uint2 w2;
+            w2.x = pack_bf16x2(ys.x, ys.y);
+            w2.y = pack_bf16x2(ys.z, ys.w);
+            *reinterpret_cast<uint2*>(nx.d_o + static_cast<long long>(row) * D + colk[k]) = w2;
+          }
         } else {
           const float4 hlf = make_float4(0.5f * d.x, 0.5f * d.y, 0.5f * d.z, 0.5f * d.w);
           *p = hlf;
@@ -300,31 +331,39 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
       }
     }
   }
-  // block reduction of dw / db: groups 1.. park their partials in shared memory, group 0 adds and publishes
-#pragma unroll
-  for (int k = 0; k < 2; ++k) {
-    if (act[k] && grp > 0) {
-      *reinterpret_cast<float4*>(&s_acc[grp - 1][0][colk[k]]) = aw[k];
-      *reinterpret_cast<float4*>(&s_acc[grp - 1][1][colk[k]]) = ab[k];
-    }
-  }
-  __syncthreads();
-  if (grp == 0) {
+  // block reduction of dw / db (then, with a tail, of dscale / dbias through the same shared buffer): groups 1..
+  // park their partials in shared memory, group 0 adds and publishes
+  auto block_reduce_publish = [&](float4* pa, float4* pb, float* outa, float* outb) {
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
-      if (act[k]) {
-        for (int g2 = 0; g2 < LNB_GROUPS - 1; ++g2) {
-          const float4 pw = *reinterpret_cast<const float4*>(&s_acc[g2][0][colk[k]]);
-          const float4 pb = *reinterpret_cast<const float4*>(&s_acc[g2][1][colk[k]]);
-          aw[k].x += pw.x; aw[k].y += pw.y; aw[k].z += pw.z; aw[k].w += pw.w;
-          ab[k].x += pb.x; ab[k].y += pb.y; ab[k].z += pb.z; ab[k].w += pb.w;
-        }
-        float* pw = dw + colk[k];
-        float* pb = db + colk[k];
-        atomicAdd(pw, aw[k].x); atomicAdd(pw + 1, aw[k].y); atomicAdd(pw + 2, aw[k].z); atomicAdd(pw + 3, aw[k].w);
-        atomicAdd(pb, ab[k].x); atomicAdd(pb + 1, ab[k].y); atomicAdd(pb + 2, ab[k].z); atomicAdd(pb + 3, ab[k].w);
+      if (act[k] && grp > 0) {
+        *reinterpret_cast<float4*>(&s_acc[grp - 1][0][colk[k]]) = pa[k];
+        *reinterpret_cast<float4*>(&s_acc[grp - 1][1][colk[k]]) = pb[k];
       }
     }
+    __syncthreads();
+    if (grp == 0) {
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        if (act[k]) {
+          for (int g2 = 0; g2 < LNB_GROUPS - 1; ++g2) {
+            const float4 qa = *reinterpret_cast<const float4*>(&s_acc[g2][0][colk[k]]);
+            const float4 qb = *reinterpret_cast<const float4*>(&s_acc[g2][1][colk[k]]);
+            pa[k].x += qa.x; pa[k].y += qa.y; pa[k].z += qa.z; pa[k].w += qa.w;
+            pb[k].x += qb.x; pb[k].y += qb.y; pb[k].z += qb.z; pb[k].w += qb.w;
+          }
+          float* oa = outa + colk[k];
+          float* ob = outb + colk[k];
+          atomicAdd(oa, pa[k].x); atomicAdd(oa + 1, pa[k].y); atomicAdd(oa + 2, pa[k].z); atomicAdd(oa + 3, pa[k].w);
+          atomicAdd(ob, pb[k].x); atomicAdd(ob + 1, pb[k].y); atomicAdd(ob + 2, pb[k].z); atomicAdd(ob + 3, pb[k].w);
+        }
+      }
+    }
+  };
+  block_reduce_publish(aw, ab, dw, db);
+  if (TAIL) {
+    __syncthreads();
+    block_reduce_publish(as2, ab2, nx.dscale, nx.dbias);
   }
 }
 
@@ -561,18 +600,44 @@ extern "C" int b200_ln_shift_fwd(const float* x, const float* x2, const float* w
   return err();
 }
 
-extern "C" int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2, const float* mean,
-                                 const float* rstd, const float* w, float* dx, float* dx2, float* dw, float* db, int M,
-                                 int D, int seq, int T, int F, int shift, int row_split, int mode, void* stream) {
+static int ln_shift_bwd_launch(const void* dh, const float* x, const float* x2, const float* mean, const float* rstd,
+                               const float* w, float* dx, float* dx2, float* dw, float* db, int M, int D, int seq,
+                               int T, int F, int shift, int row_split, int mode, const LnBwdNext& nx, void* stream) {
   if (D % 128 || D > 128 * MAXV) return -41;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
   if (D % 512 && D != 256) return -41;  // 4 warps per row: D in {256, 512, 1024}
-  int blocks = num_sms() * 2;   // persistent: two 16-warp blocks per SM
-  if (blocks * LNB_GROUPS > M) blocks = (M + LNB_GROUPS - 1) / LNB_GROUPS;
-  ln_shift_bwd_kernel<<<blocks, 128 * LNB_GROUPS, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(dh), x, x2, mean, rstd, w, dx, dx2,
-                                              dw, db, M, D, sg, mode);
+  if (nx.o && mode != 0) return -41;
+  const __nv_bfloat16* dhp = reinterpret_cast<const __nv_bfloat16*>(dh);
+  if (nx.o) {
+    int blocks = num_sms() * 2;   // persistent: two 8-warp blocks per SM (no register spills with the tail)
+    if (blocks * 2 > M) blocks = (M + 1) / 2;
+    ln_shift_bwd_kernel<2, true><<<blocks, 256, 0, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx);
+  } else {
+    int blocks = num_sms() * 3;   // persistent: three 8-warp blocks per SM
+    if (blocks * 2 > M) blocks = (M + 1) / 2;
+    ln_shift_bwd_kernel<2, false><<<blocks, 256, 0, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx);
+  }
   return err();
+}
+
+extern "C" int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2, const float* mean,
+                                 const float* rstd, const float* w, float* dx, float* dx2, float* dw, float* db, int M,
+                                 int D, int seq, int T, int F, int shift, int row_split, int mode, void* stream) {
+  LnBwdNext nx{nullptr, nullptr, nullptr, nullptr, nullptr};
+  return ln_shift_bwd_launch(dh, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, seq, T, F, shift, row_split, mode, nx,
+                             stream);
+}
+
+// mode 0 with the next block's residual prologue fused in (see LnBwdNext)
+extern "C" int b200_ln_shift_bwd_prep(const void* dh, const float* x, const float* mean, const float* rstd,
+                                      const float* w, float* dx, float* dw, float* db, const void* o_next,
+                                      const float* scale_next, void* d_o_next, float* dscale_next, float* dbias_next,
+                                      int M, int D, int seq, int T, int F, int shift, int row_split, void* stream) {
+  LnBwdNext nx{reinterpret_cast<const __nv_bfloat16*>(o_next), scale_next, reinterpret_cast<__nv_bfloat16*>(d_o_next),
+               dscale_next, dbias_next};
+  return ln_shift_bwd_launch(dh, x, nullptr, mean, rstd, w, dx, nullptr, dw, db, M, D, seq, T, F, shift, row_split, 0,
+                             nx, stream);
 }
 
 extern "C" int b200_resid_bwd_prep(const float* dy, const void* o, const float* scale, void* d_o, float* dscale,

@@ -68,9 +68,26 @@ def ln_shift_fwd(x, x2, w, b, out, mean, rstd, cfg: DalleConfig, shift: bool, ro
 
 
 def ln_shift_bwd(dh, x, x2, mean, rstd, w, dx, dx2, dw, db, cfg: DalleConfig, shift: bool, mode: int,
-                 row_split: int = 0):
-    """mode 0: dx += grad; mode 1: dx = dx2 = 0.5 grad.  dw, db accumulate."""
+                 row_split: int = 0, next_prep=None):
+    """mode 0: dx += grad; mode 1: dx = dx2 = 0.5 grad.  dw, db accumulate.
+
+    ``next_prep = (o, scale, d_o, dscale, dbias)`` (mode 0 only) additionally runs ``resid_bwd_prep`` of the block
+    the backward walk visits next on the finished ``dx`` inside the same kernel."""
     M, D = x.shape
+    if next_prep is not None:
+        assert mode == 0 and x2 is None
+        if x.is_cuda:
+            o, scale, d_o, dscale, dbias = next_prep
+            rc = lib.cuda_lib().b200_ln_shift_bwd_prep(
+                dh.data_ptr(), x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), w.data_ptr(), dx.data_ptr(),
+                dw.data_ptr(), db.data_ptr(), o.data_ptr(), scale.data_ptr(), d_o.data_ptr(), dscale.data_ptr(),
+                dbias.data_ptr(), M, D, cfg.seq_len, cfg.text_len, cfg.image_fmap_size, int(shift), row_split,
+                _stream())
+            lib.check(rc, "b200_ln_shift_bwd_prep")
+            return
+        ln_shift_bwd(dh, x, x2, mean, rstd, w, dx, dx2, dw, db, cfg, shift, mode, row_split)
+        resid_bwd_prep(dx, *next_prep)
+        return
     if not x.is_cuda:
         if row_split:
             dh = _unpermute_rows(dh, cfg, row_split)

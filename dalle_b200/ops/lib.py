@@ -117,6 +117,7 @@ class _Sigs:
     b200_attn_fwd = [_p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
     b200_ln_shift_fwd = [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _f, _p]
     b200_ln_shift_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _i, _p]
+    b200_ln_shift_bwd_prep = [_p] * 13 + [_i] * 7 + [_p]
     b200_resid_bwd_prep = [_p, _p, _p, _p, _p, _p, _i, _i, _p]
     b200_colsum_bf16 = [_p, _l, _p, _i, _i, _f, _p]
     b200_embed_fwd = [_p, _p, _p, _p, _i, _i, _p]

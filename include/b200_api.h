@@ -86,6 +86,14 @@ int b200_ln_shift_fwd(const float* x, const float* x2, const float* w, const flo
 int b200_ln_shift_bwd(const void* dh, const float* x, const float* x2, const float* mean, const float* rstd,
                       const float* w, float* dx, float* dx2, float* dw, float* db, int M, int D, int seq, int T, int F,
                       int shift, int row_split, int mode, void* stream);
+/* b200_ln_shift_bwd (mode 0) that also runs the LayerScale/residual prologue of the block the backward walk visits
+ * next on the stream gradient it has just completed: d_o_next = bf16(dx * scale_next),
+ * dscale_next += colsum(dx * o_next), dbias_next += colsum(dx * scale_next)  (what b200_resid_bwd_prep would do in a
+ * second pass over dx).  Needs o_next kept from the forward, i.e. a layer that stores its activations. */
+int b200_ln_shift_bwd_prep(const void* dh, const float* x, const float* mean, const float* rstd, const float* w,
+                           float* dx, float* dw, float* db, const void* o_next, const float* scale_next,
+                           void* d_o_next, float* dscale_next, float* dbias_next, int M, int D, int seq, int T, int F,
+                           int shift, int row_split, void* stream);
 /* LayerScale/residual backward prep: d_o(bf16) = dy*scale ; dscale += colsum(dy*o) ; dbias += colsum(dy*scale). */
 int b200_resid_bwd_prep(const float* dy, const void* o, const float* scale, void* d_o, float* dscale, float* dbias,
                         int M, int D, void* stream);

@@ -49,6 +49,9 @@ def main():
     print(f"ln_shift_fwd {timeit(lambda: E.ln_shift_fwd(x, None, w, bb, h, mean, rstd, cfg, True)):.0f} us")
     dx = torch.zeros(M, D, device=dev); dw = torch.zeros(D, device=dev); db = torch.zeros(D, device=dev)
     print(f"ln_shift_bwd {timeit(lambda: E.ln_shift_bwd(h, x, None, mean, rstd, w, dx, None, dw, db, cfg, True, 0)):.0f} us")
+    o_n = torch.randn(M, D, device=dev).bfloat16(); d_on = torch.zeros(M, D, device=dev, dtype=torch.bfloat16)
+    dsn = torch.zeros(D, device=dev); dbn = torch.zeros(D, device=dev)
+    print(f"ln_shift_bwd+prep {timeit(lambda: E.ln_shift_bwd(h, x, None, mean, rstd, w, dx, None, dw, db, cfg, True, 0, next_prep=(o_n, w, d_on, dsn, dbn))):.0f} us")
     # GEMM epilogue variants
     W1 = (torch.randn(8192, D, device=dev) * 0.03).bfloat16(); b1 = torch.zeros(8192, device=dev)
     u = torch.zeros(M, 4096, device=dev, dtype=torch.bfloat16); pre = torch.zeros(M, 8192, device=dev, dtype=torch.bfloat16)
