@@ -97,14 +97,13 @@ __device__ __forceinline__ int permuted_row32(const ShiftGeom& s, int bidx, int 
 // are reduced in the group, and the normalised values are scattered to the rows the shift sends them to (each
 // output element has exactly one writer: its source row, or - where the shift pads with zeros - the row itself).
 // ------------------------------------------------------------------------------------------------
-constexpr int LNF_GROUPS = 4;
-__global__ void __launch_bounds__(128 * LNF_GROUPS, 2)
+constexpr int LNF_GROUPS = 2;
+__global__ void __launch_bounds__(128 * LNF_GROUPS, 3)
 ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, const float* __restrict__ w,
                     const float* __restrict__ b, __nv_bfloat16* __restrict__ out, float* __restrict__ mean,
                     float* __restrict__ rstd, int M, int D, float eps, ShiftGeom sg) {
-  // persistent blocks of 4 row groups x 128 threads (<= 8 channels per thread), each group walking a contiguous
-  // range of rows; the next row's loads are issued before the current row's reductions (two register buffers in
-  // ping-pong).  (A warp-per-row variant with 8 float4 per lane measured 1.8x slower: too few loads in flight.)
+  // persistent blocks of 2 row groups x 128 threads (<= 8 channels per thread), each group walking a contiguous
+  // range of rows with its loads three rows ahead.  (A warp-per-row variant with 8 float4 per lane measured 1.8x slower: too few loads in flight.)
   __shared__ float sred[LNF_GROUPS][2][2][4];   // [group][row parity][mean / var pass][warp]
   const int grp = threadIdx.x >> 7, t128 = threadIdx.x & 127, wsub = t128 >> 5;
   const int nper = D / 512;
@@ -185,18 +184,24 @@ ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, c
     }
     ++it;
   };
-  float4 va[2], vb[2];
+  // ring of four register buffers: the loads run three rows ahead of the row being normalised (one row ahead left
+  // every iteration waiting for most of a DRAM round trip)
+  float4 v[4][2];
   if (row_begin < row_end) {   // (uniform per row group, and the group barriers are only used inside)
-    load_row(row_begin, va);
-    while (true) {
-      load_row(rw.row + 1 < row_end ? rw.row + 1 : M, vb);
-      process(va);
-      rw.next(sg);
-      if (rw.row >= row_end) break;
-      load_row(rw.row + 1 < row_end ? rw.row + 1 : M, va);
-      process(vb);
-      rw.next(sg);
-      if (rw.row >= row_end) break;
+    load_row(row_begin, v[0]);
+    load_row(row_begin + 1 < row_end ? row_begin + 1 : M, v[1]);
+    load_row(row_begin + 2 < row_end ? row_begin + 2 : M, v[2]);
+    bool done = false;
+    while (!done) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if (!done) {
+          load_row(rw.row + 3 < row_end ? rw.row + 3 : M, v[(k + 3) & 3]);
+          process(v[k]);
+          rw.next(sg);
+          done = rw.row >= row_end;
+        }
+      }
     }
   }
 }
@@ -593,7 +598,7 @@ extern "C" int b200_ln_shift_fwd(const float* x, const float* x2, const float* w
   if (D % 512 && D != 256) return -41;  // 4 warps per row: D in {256, 512, 1024}
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
-  int blocks = num_sms() * 2;   // persistent: two 16-warp blocks per SM
+  int blocks = num_sms() * 3;   // persistent: three 8-warp blocks per SM
   if (blocks * LNF_GROUPS > M) blocks = (M + LNF_GROUPS - 1) / LNF_GROUPS;
   ln_shift_fwd_kernel<<<blocks, 128 * LNF_GROUPS, 0, st>>>(x, x2, w, b, reinterpret_cast<__nv_bfloat16*>(out), mean,
                                                            rstd, M, D, eps, sg);
