@@ -316,18 +316,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       // ---- dK (part 0) / dV (part 1) of this chunk: thread = key row i of the chunk ----
       mbar_wait(bar_mma2, c & 1);
       tc_fence_after();
-      int ktok;  // token index of key row i, -1 if it must not be written
-      bool direct = false;
-      if (is_text) {
-        const int kt = c * 128 + i;
-        ktok = kt < g.T ? kt : -1;
-      } else if (MODE == ATT_ROW || MODE == ATT_COL) {
-        ktok = q_valid ? tpos : -1;  // the block's own tokens, same enumeration as the queries
-        direct = true;
-      } else {
-        const int kp = q0 - 2 * g.F + lc * 128 + i;
-        ktok = (kp >= 0 && kp < g.P - 1 && kp < q0 + 128) ? g.T + kp : -1;
-      }
+      const bool direct = !is_text && (MODE == ATT_ROW || MODE == ATT_COL);
+      // token index of key row `ri` of the chunk, -1 if it must not be written
+      auto key_tok = [&](int ri) -> int {
+        if (is_text) {
+          const int kt = c * 128 + ri;
+          return kt < g.T ? kt : -1;
+        }
+        const int kp = q0 - 2 * g.F + lc * 128 + ri;   // (conv_like local chunks; axial local chunks are `direct`)
+        return (kp >= 0 && kp < g.P - 1 && kp < q0 + 128) ? g.T + kp : -1;
+      };
+      const int ktok = direct ? (q_valid ? tpos : -1) : key_tok(i);   // axial: the block's own tokens
       if (__any_sync(0xffffffffu, ktok >= 0)) {
         const bool is_v = part == 1;
 #pragma unroll 1
@@ -336,19 +335,40 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
           uint32_t r[32];
           tmem_ld32(trow + (is_v ? TM_DV : TM_DK) + d0, r);
           tmem_ld_wait();
-          if (ktok < 0) continue;
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          const long long grow = static_cast<long long>(b) * g.seq + ktok;
           if (direct) {
+            if (ktok < 0) continue;
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            const long long grow = static_cast<long long>(b) * g.seq + ktok;
             inv_rotary32(v, a.rot_t + ktok, a.rot_len, d0, 1.0f);
             store32_bf16(a.dqkv + grow * (3 * HD) + (is_v ? 2 : 1) * HD + h * 64 + d0, v);
           } else {
-            float* dst = a.kv_acc + grow * (2 * HD) + (is_v ? HD : 0) + h * 64 + d0;
+            // shared keys: fp32 red.add into kv_acc.  Straight from the TMEM layout (lane = key row) one red.v4
+            // touches 32 different rows = 32 L1 wavefronts; the warp's own slice of the P / dS buffers (dead
+            // until the next chunk) transposes the 32 x 32 tile so that an instruction covers four whole
+            // 128-byte row segments instead.
             if (a.debug_skip_atomics) continue;
+            uint8_t* stg = (half == 0 ? sP : sDS) + part * 16384 + qw * 4096;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) red_add_v4(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+            for (int c8 = 0; c8 < 8; ++c8)
+              *reinterpret_cast<uint4*>(stg + lane * 128 + ((c8 ^ (lane & 7)) << 4)) =
+                  make_uint4(r[4 * c8], r[4 * c8 + 1], r[4 * c8 + 2], r[4 * c8 + 3]);
+            __syncwarp();
+            const int cq = lane & 7;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int rr = (lane >> 3) + 4 * it;
+              const int kt = key_tok(qw * 32 + rr);
+              const uint4 u = *reinterpret_cast<const uint4*>(stg + rr * 128 + ((cq ^ (rr & 7)) << 4));
+              if (kt >= 0) {
+                float* dst = a.kv_acc + (static_cast<long long>(b) * g.seq + kt) * (2 * HD) + (is_v ? HD : 0) +
+                             h * 64 + d0 + cq * 4;
+                red_add_v4(dst, __uint_as_float(u.x), __uint_as_float(u.y), __uint_as_float(u.z),
+                           __uint_as_float(u.w));
+              }
+            }
+            __syncwarp();
           }
         }
       }
