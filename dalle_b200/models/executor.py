@@ -298,8 +298,7 @@ class Engine:
                 if train:
                     dl = lg[:, :nv]
                     G.gemm(G.NN, G.EPI_BF16, dl, Wseg, b.dhf[row0 + r0: row0 + r0 + r])
-                    G.gemm(G.TN, G.EPI_ATOMIC_F32, dl, hrows, gW[v0:v0 + nv])
-                    E.colsum(dl, gb[v0:v0 + nv])
+                    G.gemm(G.TN, G.EPI_ATOMIC_F32, dl, hrows, gW[v0:v0 + nv], a_colsum=gb[v0:v0 + nv])
 
     def final_norm(self, b):
         m, cfg = self.model, self.cfg
@@ -340,8 +339,8 @@ class Engine:
             E.resid_bwd_prep(b.dx2, o, sg.view(-1), b.d_o, self.grad_of(sg).view(-1), self.grad_of(m.ff_b2[f]))
         G.gemm(G.TN, G.EPI_ATOMIC_F32, b.d_o, u, self.grad_of(m.ff_w2[f]))
         G.gemm(G.NN, G.EPI_GEGLU_BWD, b.d_o, self.w(m.ff_w2[f]), b.dpre, aux=pre, n_half=hid)
-        E.colsum(b.dpre, self.grad_of(m.ff_b1[f]))
-        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dpre, h, self.grad_of(m.ff_w1[f]))
+        # dW1 and db1 from one pass over d_pre (the bias gradient is summed from the A tiles inside the wgrad GEMM)
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, b.dpre, h, self.grad_of(m.ff_w1[f]), a_colsum=self.grad_of(m.ff_b1[f]))
         G.gemm(G.NN, G.EPI_BF16, b.dpre, self.w(m.ff_w1[f]), b.dh)
         nxt = self._next_prep_f(i, b)
         E.ln_shift_bwd(b.dh, x1, None, mean, rstd, m.norm_g_w[i], b.dx1, None, self.grad_of(m.norm_g_w[i]),

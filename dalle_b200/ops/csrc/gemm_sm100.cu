@@ -35,7 +35,11 @@ __host__ __device__ constexpr int gemm_stages(int epi) {
 // epilogue: no gain.  An ablation showed why: that kernel's time is its 1.3 GB of epilogue loads + stores, whose
 // in-flight volume is capped by the 64 KB of staging left beside the mainloop stages, not the epilogue math.)
 __host__ __device__ constexpr int gemm_epi_warps(int epi) { return 8; }
-__host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * gemm_epi_warps(epi); }  // + TMA, MMA warps
+// + TMA, MMA warps; the accumulating (wgrad) kernel has two more warps that can sum the A tiles (see GemmDev::a_colsum)
+__host__ __device__ constexpr int gemm_sum_warps(int epi) { return epi == B200_EPI_ATOMIC_F32 ? 2 : 0; }
+__host__ __device__ constexpr int gemm_threads(int epi) {
+  return 64 + 32 * gemm_epi_warps(epi) + 32 * gemm_sum_warps(epi);
+}
 __host__ __device__ constexpr int gemm_out_tiles(int epi) {   // staging tiles per epilogue warp
   return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? (gemm_epi_warps(epi) == 16 ? 2 : 4) : (epi == B200_EPI_RESID ? 5 : 2));
 }
@@ -43,7 +47,7 @@ __host__ __device__ constexpr int gemm_out_stage_bytes(int epi) {
   return gemm_epi_warps(epi) * gemm_out_tiles(epi) * OUT_TILE_BYTES;
 }
 __host__ __device__ constexpr int gemm_smem_bytes(int epi) {
-  return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 512 /*barriers*/;
+  return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 1024 /*barriers, column-sum scratch*/;
 }
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 
@@ -66,6 +70,7 @@ struct GemmDev {
   const __nv_bfloat16* aux;  long long ldaux;
   int n_half;
   float alpha;
+  float* a_colsum;     // TN only: a_colsum[m] += sum_k A[k, m], taken from the A tiles in shared memory
 };
 
 // The i-th work unit of this CTA: output tile t, k-blocks [kb0, kb1).
@@ -206,7 +211,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 32 * gemm_epi_warps(EPI));
     }
-    if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID)
+    if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == B200_EPI_ATOMIC_F32)
       for (int s = 0; s < 2 * gemm_epi_warps(EPI); ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
@@ -286,6 +291,80 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         umma_commit(&tfull_bar[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else if (gemm_sum_warps(EPI) > 0 && warp >= 2 + gemm_epi_warps(EPI)) {
+    // ------------------------------- A column sums (TN wgrad + bias gradient) -------------------
+    // dW = A^T B reads A = d(pre-activation) [K rows, M columns]; the matching bias gradient is the column sum of
+    // the same matrix.  Two extra warps fetch A boxes ({64 k} x {64 m}, 8 KB) through their OWN double-buffered
+    // TMA loads - L2 hits, the mainloop pulls the same panel at the same time - and sum them.  (Reading the
+    // mainloop's stages instead put these warps on the stage-release path: +20 % kernel time even with empty
+    // loops.)  The n_tiles units that share an A panel take its k-blocks in turn.
+    if (A_MN == 1 && EPI == B200_EPI_ATOMIC_F32 && g.a_colsum) {
+      const int box = warp - (2 + gemm_epi_warps(EPI));
+      float* s_cs = reinterpret_cast<float*>(bars + 64) + box * 64;   // this warp's 64 column sums of a unit
+      uint8_t* buf = smem_out + box * 16384;                          // 2 x 8 KB (the staging space is unused here)
+      uint64_t* lbar = aux_bar + box * 2;
+      s_cs[lane] = 0.f;
+      s_cs[lane + 32] = 0.f;
+      __syncwarp();
+      uint32_t n_ld = 0, n_use = 0;   // boxes requested / consumed: buffer = n & 1, parity = (n >> 1) & 1
+      GemmUnit un;
+      for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
+        const int n_blk = un.t % g.n_tiles, m_blk = un.t / g.n_tiles;
+        const int mcol = m_blk * BM + box * 64;
+        // first k-block of this unit that falls to it: kb = n_blk (mod n_tiles)
+        int kb_first = un.kb0 + ((n_blk - un.kb0 % g.n_tiles) + g.n_tiles) % g.n_tiles;
+        float acc[2][8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[0][e] = acc[1][e] = 0.f;
+        auto request = [&](int kb) {
+          if (lane == 0) {
+            mbar_expect_tx(&lbar[n_ld & 1], 8192);
+            tma_load_2d(buf + (n_ld & 1) * 8192, &tmA, &lbar[n_ld & 1], mcol, kb * BK);
+          }
+          ++n_ld;
+        };
+        if (kb_first < un.kb1 && mcol < g.M) {
+          request(kb_first);
+          for (int kb = kb_first; kb < un.kb1; kb += g.n_tiles) {
+            if (kb + g.n_tiles < un.kb1) request(kb + g.n_tiles);   // the other buffer: consumed one step ago
+            mbar_wait(&lbar[n_use & 1], (n_use >> 1) & 1);
+            // a lane reads the 16-byte cell (lane & 7) of rows (lane >> 3) + 4 i; the swizzle puts logical cell
+            // (lane & 7) ^ (row & 7) there, and row & 7 takes two values per lane -> two sets of 8 partial sums
+            const uint8_t* tile = buf + (n_use & 1) * 8192 + (lane >> 3) * 128 + ((lane & 7) << 4);
+            ++n_use;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const uint4 u = *reinterpret_cast<const uint4*>(tile + i * 512);
+              float* a_ = acc[i & 1];
+              float2 f;
+              f = unpack_bf16x2(u.x); a_[0] += f.x; a_[1] += f.y;
+              f = unpack_bf16x2(u.y); a_[2] += f.x; a_[3] += f.y;
+              f = unpack_bf16x2(u.z); a_[4] += f.x; a_[5] += f.y;
+              f = unpack_bf16x2(u.w); a_[6] += f.x; a_[7] += f.y;
+            }
+            __syncwarp();   // all lanes are done with the buffer before it is requested again
+          }
+          // unit done: fold the lanes' partials in shared memory, then one global atomic per column
+          // (rows past K and columns past M were zero-filled by TMA)
+#pragma unroll
+          for (int par = 0; par < 2; ++par) {
+            const int row7 = ((lane >> 3) + 4 * par) & 7;            // row & 7 of the rows behind acc[par]
+            const int cell = (lane & 7) ^ row7;                      // logical 16-byte cell = 8 m columns
+#pragma unroll
+            for (int e = 0; e < 8; ++e) atomicAdd(&s_cs[cell * 8 + e], acc[par][e]);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int m = mcol + lane + 32 * e;
+            const float v = s_cs[lane + 32 * e];
+            s_cs[lane + 32 * e] = 0.f;
+            if (m < g.M && v != 0.f) atomicAdd(g.a_colsum + m, v);
+          }
+          __syncwarp();
+        }
       }
     }
   } else {
@@ -786,6 +865,8 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   g.aux = reinterpret_cast<const __nv_bfloat16*>(d->aux); g.ldaux = d->ldaux;
   g.n_half = d->n_half;
   g.alpha = d->alpha;
+  if (d->a_colsum && !(a_mn && d->epi == B200_EPI_ATOMIC_F32)) return -16;
+  g.a_colsum = d->a_colsum;
 
   // output maps for the TMA-store epilogues
   g_tm_out = ta;

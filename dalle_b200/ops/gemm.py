@@ -109,9 +109,12 @@ def gemm_ref(mode, epi, A, B, out, *, out2=None, bias=None, scale=None, res=None
 
 def gemm(mode: int, epi: int, A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, *, out2=None, bias=None,
          scale=None, res=None, rot=None, seq_len: int = 0, q_cols: int = 0, q_scale: float = 1.0, aux=None,
-         n_half: int = 0, alpha: float = 1.0, splits: int = 0, pos_ptr=None):
-    """out = epilogue(A (x) B).  Shapes by mode: NT A[M,K] B[N,K]; NN A[M,K] B[K,N]; TN A[K,M] B[K,N]."""
+         n_half: int = 0, alpha: float = 1.0, splits: int = 0, pos_ptr=None, a_colsum=None):
+    """out = epilogue(A (x) B).  Shapes by mode: NT A[M,K] B[N,K]; NN A[M,K] B[K,N]; TN A[K,M] B[K,N].
+    ``a_colsum`` (TN + EPI_ATOMIC_F32): fp32 [M] that additionally receives the column sums of A."""
     if not A.is_cuda:
+        if a_colsum is not None:
+            a_colsum.view(-1).add_(A.float().sum(0))
         return gemm_ref(mode, epi, A, B, out, out2=out2, bias=bias, scale=scale, res=res, rot=rot, seq_len=seq_len,
                         q_cols=q_cols, q_scale=q_scale, aux=aux, n_half=n_half, alpha=alpha)
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
@@ -144,6 +147,9 @@ def gemm(mode: int, epi: int, A: torch.Tensor, B: torch.Tensor, out: torch.Tenso
     d.pos_ptr = _ptr(pos_ptr)
     d.aux, d.ldaux = _ptr(aux), _ld(aux)
     d.n_half, d.alpha, d.splits = n_half, alpha, splits
+    if a_colsum is not None:
+        assert mode == TN and epi == EPI_ATOMIC_F32 and a_colsum.dtype == torch.float32 and a_colsum.numel() == M
+    d.a_colsum = _ptr(a_colsum)
     rc = lib.cuda_lib().b200_gemm_bf16(ctypes.byref(d), torch.cuda.current_stream().cuda_stream)
     lib.check(rc, "b200_gemm_bf16")
     return out

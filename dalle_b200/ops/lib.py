@@ -31,6 +31,7 @@ class B200Gemm(ctypes.Structure):
         ("pos_ptr", ctypes.c_void_p),
         ("aux", ctypes.c_void_p), ("ldaux", ctypes.c_longlong),
         ("n_half", ctypes.c_int), ("alpha", ctypes.c_float), ("splits", ctypes.c_int),
+        ("a_colsum", ctypes.c_void_p),
     ]
 
 

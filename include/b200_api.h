@@ -50,6 +50,8 @@ typedef struct B200Gemm {
   int n_half;          /* GEGLU: N counts value columns only; B has 2*n_half rows */
   float alpha;
   int splits;          /* 0 = auto (only ATOMIC_F32 may split) */
+  float* a_colsum;     /* TN + ATOMIC_F32 only, or NULL: a_colsum[m] += sum_k A[k, m] (the bias gradient that goes
+                          with a weight gradient), summed from the A tiles while they sit in shared memory */
 } B200Gemm;
 
 int b200_gemm_bf16(const B200Gemm* desc, void* stream);

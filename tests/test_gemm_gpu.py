@@ -97,3 +97,15 @@ def test_rotary_epilogue():
     ref = torch.empty(M, N)
     G.gemm_ref(G.NT, G.EPI_ROTARY, A.cpu(), W.cpu(), ref, rot=rot.cpu(), seq_len=seq, q_cols=128, q_scale=0.125)
     _check(out.cpu(), ref)
+
+
+def test_wgrad_with_fused_bias_gradient():
+    """TN accumulate GEMM that also returns the column sums of A (dW and db from one pass over d_pre)."""
+    K, M, N = 1000, 640, 512          # K not a multiple of 64, M spans several tiles
+    A, B = _rand(K, M), _rand(K, N)
+    out = torch.zeros(M, N, device="cuda")
+    cs = torch.full((M,), 0.5, device="cuda")
+    G.gemm(G.TN, G.EPI_ATOMIC_F32, A, B, out, a_colsum=cs)
+    _check(out.cpu(), A.float().cpu().t() @ B.float().cpu(), tol=5e-3)
+    ref = 0.5 + A.float().sum(0).cpu()
+    assert (cs.cpu() - ref).abs().max().item() < 2e-3 * ref.abs().max().item() + 1e-3

@@ -74,6 +74,9 @@ def main():
     gW1 = torch.zeros(8192, D, device=dev)
     t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, dpre, h, gW1))
     print(f"wgrad FF1        {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
+    db1 = torch.zeros(8192, device=dev)
+    t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, dpre, h, gW1, a_colsum=db1))
+    print(f"wgrad FF1 + db   {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
     gWo = torch.zeros(D, D, device=dev)
     t_ = timeit(lambda: G.gemm(G.TN, G.EPI_ATOMIC_F32, d_o, h, gWo))
     print(f"wgrad 1024x1024  {t_:.0f} us  {2*M*D*D/t_/1e6:.0f} TF/s")
