@@ -60,7 +60,7 @@ def main():
     t_ = timeit(lambda: G.gemm(G.NT, G.EPI_GEGLU, h, W1, u, bias=b1, n_half=4096))
     print(f"FF1 GEGLU        {t_:.0f} us  {2*M*8192*D/t_/1e6:.0f} TF/s")
     W2 = (torch.randn(D, 4096, device=dev) * 0.03).bfloat16(); sc = torch.ones(D, device=dev)
-    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_RESID, u, W2, x, bias=bb, scale=sc, res=x, alpha=1.0))
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_RESID, u, W2, x, out2=h, bias=bb, scale=sc, res=x, alpha=1.0))
     print(f"FF2 RESID        {t_:.0f} us  {2*M*4096*D/t_/1e6:.0f} TF/s")
     Wq = (torch.randn(3 * I, D, device=dev) * 0.03).bfloat16()
     t_ = timeit(lambda: G.gemm(G.NT, G.EPI_ROTARY, h, Wq, qkv[:M], rot=rot, seq_len=cfg.seq_len, q_cols=I, q_scale=0.125))
@@ -82,7 +82,7 @@ def main():
     print(f"wgrad 1024x1024  {t_:.0f} us  {2*M*D*D/t_/1e6:.0f} TF/s")
     # the remaining per-layer shapes
     Wo = (torch.randn(D, I, device=dev) * 0.03).bfloat16(); ao = torch.randn(M, I, device=dev).bfloat16()
-    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_RESID, ao, Wo, x, bias=bb, scale=sc, res=x, alpha=1.0))
+    t_ = timeit(lambda: G.gemm(G.NT, G.EPI_RESID, ao, Wo, x, out2=h, bias=bb, scale=sc, res=x, alpha=1.0))
     print(f"out-proj RESID   {t_:.0f} us  {2*M*I*D/t_/1e6:.0f} TF/s")
     dao = torch.zeros(M, I, device=dev, dtype=torch.bfloat16)
     t_ = timeit(lambda: G.gemm(G.NN, G.EPI_BF16, d_o, Wo, dao))
