@@ -427,29 +427,47 @@ __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __n
 // kv_acc (fp32, rot domain) -> inverse rotary -> bf16 into d_qkv k/v sections; clears kv_acc.
 // rows_per_sample = T (axial: only text keys went through the accumulator) or seq (conv_like).
 // thread = 8 consecutive columns (4 rotary pairs) of one row.
+constexpr int FIN_ROWS = 4;   // rows per thread: all loads of the four rows are issued before the first use
 __global__ void __launch_bounds__(256)
 attn_bwd_finish_kernel(float* __restrict__ kv_acc, __nv_bfloat16* __restrict__ dqkv, const float2* __restrict__ rot,
                        int B, int seq, int rows_per_sample, int HD) {
   const int groups_per_row = (2 * HD) / 8;
-  const unsigned total = static_cast<unsigned>(B) * rows_per_sample * groups_per_row;
+  const unsigned n_rows = static_cast<unsigned>(B) * rows_per_sample;
+  const unsigned row_groups = (n_rows + FIN_ROWS - 1) / FIN_ROWS;
   const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const unsigned gcol = idx % groups_per_row, rr = idx / groups_per_row;
-  const int t = rr % rows_per_sample, b = rr / rows_per_sample;
-  const long long grow = static_cast<long long>(b) * seq + t;
+  if (idx >= row_groups * groups_per_row) return;
+  const unsigned gcol = idx % groups_per_row, rg = idx / groups_per_row;
   const int col = gcol * 8;
-  float4* src = reinterpret_cast<float4*>(kv_acc + grow * (2 * HD) + col);
-  const float4 a = src[0], c = src[1];
-  src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-  src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-  const float4* rt = reinterpret_cast<const float4*>(rot + static_cast<long long>(t) * 32 + ((col & 63) >> 1));
-  const float4 r01 = __ldg(rt), r23 = __ldg(rt + 1);  // (cos0, sin0, cos1, sin1), (cos2, sin2, cos3, sin3)
-  uint4 o;
-  o.x = pack_bf16x2(a.x * r01.x + a.y * r01.y, a.y * r01.x - a.x * r01.y);
-  o.y = pack_bf16x2(a.z * r01.z + a.w * r01.w, a.w * r01.z - a.z * r01.w);
-  o.z = pack_bf16x2(c.x * r23.x + c.y * r23.y, c.y * r23.x - c.x * r23.y);
-  o.w = pack_bf16x2(c.z * r23.z + c.w * r23.w, c.w * r23.z - c.z * r23.w);
-  *reinterpret_cast<uint4*>(dqkv + grow * (3 * HD) + HD + col) = o;
+  float4 a[FIN_ROWS], c[FIN_ROWS], r01[FIN_ROWS], r23[FIN_ROWS];
+  long long grow[FIN_ROWS];
+  bool ok[FIN_ROWS];
+#pragma unroll
+  for (int j = 0; j < FIN_ROWS; ++j) {
+    const unsigned rr = rg * FIN_ROWS + j;
+    ok[j] = rr < n_rows;
+    const unsigned rs = ok[j] ? rr : 0u;
+    const int t = rs % rows_per_sample, b = rs / rows_per_sample;
+    grow[j] = static_cast<long long>(b) * seq + t;
+    const float4* src = reinterpret_cast<const float4*>(kv_acc + grow[j] * (2 * HD) + col);
+    a[j] = src[0];
+    c[j] = src[1];
+    const float4* rt = reinterpret_cast<const float4*>(rot + static_cast<long long>(t) * 32 + ((col & 63) >> 1));
+    r01[j] = __ldg(rt);        // (cos0, sin0, cos1, sin1)
+    r23[j] = __ldg(rt + 1);    // (cos2, sin2, cos3, sin3)
+  }
+#pragma unroll
+  for (int j = 0; j < FIN_ROWS; ++j) {
+    if (!ok[j]) continue;
+    float4* src = reinterpret_cast<float4*>(kv_acc + grow[j] * (2 * HD) + col);
+    src[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    src[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4 o;
+    o.x = pack_bf16x2(a[j].x * r01[j].x + a[j].y * r01[j].y, a[j].y * r01[j].x - a[j].x * r01[j].y);
+    o.y = pack_bf16x2(a[j].z * r01[j].z + a[j].w * r01[j].w, a[j].w * r01[j].z - a[j].z * r01[j].w);
+    o.z = pack_bf16x2(c[j].x * r23[j].x + c[j].y * r23[j].y, c[j].y * r23[j].x - c[j].x * r23[j].y);
+    o.w = pack_bf16x2(c[j].z * r23[j].z + c[j].w * r23[j].w, c[j].w * r23[j].z - c[j].z * r23[j].w);
+    *reinterpret_cast<uint4*>(dqkv + grow[j] * (3 * HD) + HD + col) = o;
+  }
 }
 
 template <int MODE>
@@ -515,7 +533,8 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   }
   if (rc) return rc;
   const int rows_per_sample = (mode == ATT_CONV) ? seq : T;
-  const long long total = static_cast<long long>(B) * rows_per_sample * (2 * HD / 8);
+  const long long total =
+      (static_cast<long long>(B) * rows_per_sample + FIN_ROWS - 1) / FIN_ROWS * (2 * HD / 8);
   if (total >= (1ll << 32)) return -24;
   const int threads = 256;
   const long long blocks = (total + threads - 1) / threads;
