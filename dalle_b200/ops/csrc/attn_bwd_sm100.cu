@@ -28,7 +28,7 @@ constexpr int ATTB_THREADS = 320;   // TMA warp, MMA warp, 8 worker warps
 struct AttnBwdArgs {
   AttnGeom g;
   const float* lse;     // [B,H,seq] log2 domain
-  const float* delta;   // [B,H,seq] rowsum(dO * O)
+  const __nv_bfloat16* out;  // forward output [B*seq, H*64] (delta = rowsum(dO * O) is formed in the kernel)
   __nv_bfloat16* dqkv;  // [B*seq, 3*H*64]
   float* kv_acc;        // [B*seq, 2*H*64] fp32, zero on entry
   const float2* rot;    // [seq+1][32] (cos, sin)
@@ -224,7 +224,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
     }
     const long long bh = static_cast<long long>(b) * g.H + h;
     const float lse_i = q_valid ? a.lse[bh * g.seq + tpos] : 0.f;
-    const float delta_i = q_valid ? a.delta[bh * g.seq + tpos] : 0.f;
+    // delta_i = sum_d dO[i, d] * O[i, d]: O row straight from global (one 128-byte line per thread), dO row from the
+    // swizzled smem tile the MMAs use
+    float delta_i = 0.f;
+    {
+      uint4 ov[8];
+      const uint4* op = reinterpret_cast<const uint4*>(a.out + (static_cast<long long>(b) * g.seq + (q_valid ? tpos : 0)) * HD + h * 64);
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) ov[c8] = q_valid ? __ldg(op + c8) : make_uint4(0u, 0u, 0u, 0u);
+      mbar_wait(bar_q, 0);
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) {
+        const uint4 dv = *reinterpret_cast<const uint4*>(sDO + sw128_offset(i, c8));
+        float2 x, y;
+        x = unpack_bf16x2(ov[c8].x); y = unpack_bf16x2(dv.x); delta_i += x.x * y.x + x.y * y.y;
+        x = unpack_bf16x2(ov[c8].y); y = unpack_bf16x2(dv.y); delta_i += x.x * y.x + x.y * y.y;
+        x = unpack_bf16x2(ov[c8].z); y = unpack_bf16x2(dv.z); delta_i += x.x * y.x + x.y * y.y;
+        x = unpack_bf16x2(ov[c8].w); y = unpack_bf16x2(dv.w); delta_i += x.x * y.x + x.y * y.y;
+      }
+    }
     const int win0 = qw * 32;
     // validity bits of the local keys this row can see, relative to win0 (same construction as the forward)
     uint32_t lmask[3] = {0u, 0u, 0u};
@@ -398,32 +416,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   }
 }
 
-// delta[b,h,t] = sum_d dO[b,t,h,d] * O[b,t,h,d]        (8 lanes x 16 B per (row, head))
-__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
-                                  float* __restrict__ delta, int rows, int H, int seq) {
-  const long long gid = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
-  const long long grp = gid >> 3;  // (row, head)
-  const int sub = static_cast<int>(gid & 7);
-  if (grp >= static_cast<long long>(rows) * H) return;
-  const int row = static_cast<int>(grp / H), h = static_cast<int>(grp - static_cast<long long>(row) * H);
-  const long long off = static_cast<long long>(row) * H * 64 + h * 64 + sub * 8;
-  const uint4 x = *reinterpret_cast<const uint4*>(o + off);
-  const uint4 y = *reinterpret_cast<const uint4*>(d_o + off);
-  float2 a, b;
-  float s = 0.f;
-  a = unpack_bf16x2(x.x); b = unpack_bf16x2(y.x); s += a.x * b.x + a.y * b.y;
-  a = unpack_bf16x2(x.y); b = unpack_bf16x2(y.y); s += a.x * b.x + a.y * b.y;
-  a = unpack_bf16x2(x.z); b = unpack_bf16x2(y.z); s += a.x * b.x + a.y * b.y;
-  a = unpack_bf16x2(x.w); b = unpack_bf16x2(y.w); s += a.x * b.x + a.y * b.y;
-  s += __shfl_xor_sync(0xffffffffu, s, 4);
-  s += __shfl_xor_sync(0xffffffffu, s, 2);
-  s += __shfl_xor_sync(0xffffffffu, s, 1);
-  if (sub == 0) {
-    const int b_ = row / seq, t = row - b_ * seq;
-    delta[(static_cast<long long>(b_) * H + h) * seq + t] = s;
-  }
-}
-
 // kv_acc (fp32, rot domain) -> inverse rotary -> bf16 into d_qkv k/v sections; clears kv_acc.
 // rows_per_sample = T (axial: only text keys went through the accumulator) or seq (conv_like).
 // thread = 8 consecutive columns (4 rotary pairs) of one row.
@@ -495,16 +487,8 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const int HD = H * 64;
-  {
-    const long long groups = static_cast<long long>(B) * seq * H;
-    const int threads = 256;
-    const long long blocks = (groups * 8 + threads - 1) / threads;
-    attn_delta_kernel<<<static_cast<unsigned>(blocks), threads, 0, st>>>(
-        reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B * seq, H,
-        seq);
-  }
   AttnBwdArgs a;
-  a.g = g; a.lse = lse; a.delta = delta; a.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv); a.kv_acc = kv_acc;
+  a.g = g; a.lse = lse; a.out = reinterpret_cast<const __nv_bfloat16*>(out); (void)delta; a.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv); a.kv_acc = kv_acc;
   a.rot = reinterpret_cast<const float2*>(rot); a.q_scale = q_scale;
   a.rot_t = reinterpret_cast<const float2*>(rot_t); a.rot_len = seq + 1;
   a.debug_skip_atomics = getenv("B200_ATTN_SKIP_KV_ATOMICS") != nullptr;

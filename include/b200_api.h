@@ -67,7 +67,7 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq,
 
 /* Backward of b200_attn_fwd.  d_out: bf16 [B*seq (+1 padding row), H*64].  Writes dqkv bf16 [B*seq, 3*H*64] =
  * gradient w.r.t. the RAW projection output (inverse rotary and the q scale are applied inside).
- * Scratch: delta fp32 [B,H,seq]; kv_acc fp32 [B*seq, 2*H*64] which must be all-zero on entry and is returned
+ * Scratch: delta (unused since delta = rowsum(dO*O) is formed inside the kernel; kept for ABI stability); kv_acc fp32 [B*seq, 2*H*64] which must be all-zero on entry and is returned
  * all-zero (gradients of keys shared between CTAs are reduced there with red.add before conversion). */
 int b200_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
                   float* kv_acc, const void* rot /* [seq+1][32] */, const void* rot_t /* [32][seq+1] */, float q_scale, int B, int H, int seq, int T, int F, int mode,
