@@ -101,7 +101,7 @@ constexpr int LNF_GROUPS = 2;
 __global__ void __launch_bounds__(128 * LNF_GROUPS, 3)
 ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, const float* __restrict__ w,
                     const float* __restrict__ b, __nv_bfloat16* __restrict__ out, float* __restrict__ mean,
-                    float* __restrict__ rstd, int M, int D, float eps, ShiftGeom sg) {
+                    float* __restrict__ rstd, int M, int D, float eps, ShiftGeom sg, int ring_rows) {
   // persistent blocks of 2 row groups x 128 threads (<= 8 channels per thread), each group walking a contiguous
   // range of rows with its loads three rows ahead.  (A warp-per-row variant with 8 float4 per lane measured 1.8x slower: too few loads in flight.)
   __shared__ float sred[LNF_GROUPS][2][2][4];   // [group][row parity][mean / var pass][warp]
@@ -140,6 +140,9 @@ ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, c
   rw.init(sg, row_begin);
   const float inv_d = 1.0f / D;
   int it = 0;
+  int refill_row = -1;
+  uint8_t* refill_dst = nullptr;
+  uint64_t* refill_bar = nullptr;
   auto process = [&](const float4* v) {
     const int row = rw.row;
     float* red = &sred[grp][it & 1][0][0];
@@ -147,6 +150,10 @@ ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, c
     s = warp_sum(s);
     if ((threadIdx.x & 31) == 0) red[wsub] = s;
     asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+    if (refill_row >= 0 && t128 == 0) {   // bulk-ring path: every thread of the group has read this row's slot
+      mbar_expect_tx(refill_bar, D * 4);
+      bulk_copy_g2s(refill_dst, x + static_cast<long long>(refill_row) * D, D * 4, refill_bar);
+    }
     const float mu = ((red[0] + red[1]) + (red[2] + red[3])) * inv_d;
     float q = 0.f;
 #pragma unroll
@@ -184,8 +191,46 @@ ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, c
     }
     ++it;
   };
-  // ring of four register buffers: the loads run three rows ahead of the row being normalised (one row ahead left
-  // every iteration waiting for most of a DRAM round trip)
+  if (ring_rows > 0) {
+    // Rows arrive by bulk async copies into a shared-memory ring, `ring_rows` rows ahead: the bytes in flight live
+    // in shared memory instead of registers (a register ring three rows deep left HBM half idle).  A slot is
+    // refilled right after the group's first barrier of the row that used it (every thread has read it by then).
+    extern __shared__ __align__(128) uint8_t ring_raw[];
+    uint8_t* ring = ring_raw + static_cast<size_t>(grp) * ring_rows * D * 4;
+    uint64_t* rbar = reinterpret_cast<uint64_t*>(ring_raw + static_cast<size_t>(LNF_GROUPS) * ring_rows * D * 4) +
+                     grp * ring_rows;
+    if (t128 == 0) {
+      for (int s_ = 0; s_ < ring_rows; ++s_) mbar_init(&rbar[s_], 1);
+      fence_barrier_init();
+    }
+    asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+    if (row_begin < row_end) {
+      if (t128 == 0) {
+        for (int s_ = 0; s_ < ring_rows && row_begin + s_ < row_end; ++s_) {
+          mbar_expect_tx(&rbar[s_], D * 4);
+          bulk_copy_g2s(ring + static_cast<size_t>(s_) * D * 4, x + static_cast<long long>(row_begin + s_) * D, D * 4,
+                        &rbar[s_]);
+        }
+      }
+      int slot = 0;
+      uint32_t par = 0;
+      for (; rw.row < row_end; rw.next(sg)) {
+        mbar_wait(&rbar[slot], par);
+        float4 v[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+          v[k] = act[k] ? *reinterpret_cast<const float4*>(ring + static_cast<size_t>(slot) * D * 4 + colk[k] * 4)
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+        refill_row = rw.row + ring_rows < row_end ? rw.row + ring_rows : -1;
+        refill_dst = ring + static_cast<size_t>(slot) * D * 4;
+        refill_bar = &rbar[slot];
+        process(v);
+        if (++slot == ring_rows) { slot = 0; par ^= 1; }
+      }
+    }
+    return;
+  }
+  // register path (final norm over the mean of two streams): ring of four register buffers, loads three rows ahead
   float4 v[4][2];
   if (row_begin < row_end) {   // (uniform per row group, and the group barriers are only used inside)
     load_row(row_begin, v[0]);
@@ -203,6 +248,103 @@ ln_shift_fwd_kernel(const float* __restrict__ x, const float* __restrict__ x2, c
         }
       }
     }
+  }
+}
+
+// Warp-per-row variant for the layer norms inside the stack (single input stream).  One warp owns a contiguous range
+// of rows and a private shared-memory ring that bulk async copies fill LNW_RING rows ahead, so the per-row cost is
+// pure warp work (no block barriers, ~3x fewer instructions per byte than 128 threads per row) and the bytes in
+// flight do not occupy registers.
+constexpr int LNW_WARPS = 8, LNW_RING = 1;
+__global__ void __launch_bounds__(32 * LNW_WARPS, 4)
+ln_shift_fwd_warp_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                         __nv_bfloat16* __restrict__ out, float* __restrict__ mean, float* __restrict__ rstd, int M,
+                         int D, float eps, ShiftGeom sg) {
+  extern __shared__ __align__(128) uint8_t ring_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nv = D / 128;
+  const size_t row_bytes = static_cast<size_t>(D) * 4;
+  uint8_t* ring = ring_raw + static_cast<size_t>(warp) * LNW_RING * row_bytes;
+  uint64_t* rbar = reinterpret_cast<uint64_t*>(ring_raw + static_cast<size_t>(LNW_WARPS) * LNW_RING * row_bytes) +
+                   warp * LNW_RING;
+  float* s_w = reinterpret_cast<float*>(ring_raw + static_cast<size_t>(LNW_WARPS) * LNW_RING * row_bytes +
+                                        LNW_WARPS * LNW_RING * 8);
+  float* s_b = s_w + D;
+  for (int c = threadIdx.x; c < D; c += blockDim.x) { s_w[c] = w[c]; s_b[c] = b[c]; }
+  if (lane == 0) {
+    for (int s_ = 0; s_ < LNW_RING; ++s_) mbar_init(&rbar[s_], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  // rows are dealt round-robin to the warps of the grid: at any moment the grid reads one contiguous window of x
+  const int warps_total = gridDim.x * LNW_WARPS;
+  const int row_begin = blockIdx.x * LNW_WARPS + warp, row_end = M;
+  if (row_begin >= row_end) return;
+  if (lane == 0) {
+    for (int s_ = 0; s_ < LNW_RING && row_begin + s_ * warps_total < row_end; ++s_) {
+      mbar_expect_tx(&rbar[s_], static_cast<uint32_t>(row_bytes));
+      bulk_copy_g2s(ring + s_ * row_bytes, x + static_cast<long long>(row_begin + s_ * warps_total) * D,
+                    static_cast<uint32_t>(row_bytes), &rbar[s_]);
+    }
+  }
+  const float inv_d = 1.0f / D;
+  int slot = 0;
+  uint32_t par = 0;
+  for (int row = row_begin; row < row_end; row += warps_total) {
+    RowWalk rw;
+    rw.init(sg, row);
+    mbar_wait(&rbar[slot], par);
+    float4 v[MAXV];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < MAXV; ++k) {
+      v[k] = k < nv ? *reinterpret_cast<const float4*>(ring + slot * row_bytes + (k * 128 + lane * 4) * 4)
+                    : make_float4(0.f, 0.f, 0.f, 0.f);
+      s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
+    }
+    __syncwarp();   // every lane has read the slot: refill it with the row LNW_RING ahead
+    if (lane == 0 && rw.row + LNW_RING * warps_total < row_end) {
+      mbar_expect_tx(&rbar[slot], static_cast<uint32_t>(row_bytes));
+      bulk_copy_g2s(ring + slot * row_bytes, x + static_cast<long long>(rw.row + LNW_RING * warps_total) * D,
+                    static_cast<uint32_t>(row_bytes), &rbar[slot]);
+    }
+    const float mu = warp_sum(s) * inv_d;
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < MAXV; ++k) {
+      if (k < nv) {
+        const float a = v[k].x - mu, c = v[k].y - mu, d = v[k].z - mu, e = v[k].w - mu;
+        q += a * a + c * c + d * d + e * e;
+      }
+    }
+    const float rs = rsqrtf(warp_sum(q) * inv_d + eps);
+    if (lane == 0) {
+      mean[rw.row] = mu;
+      rstd[rw.row] = rs;
+    }
+    const ShiftRoute rt = shift_route(sg, rw);
+    __nv_bfloat16* const o_self = out + static_cast<long long>(permuted_row32(sg, rw.bidx, rw.t)) * D;
+    __nv_bfloat16* const o_q0 = rt.dst[0] >= 0 ? out + static_cast<long long>(permuted_row32(sg, rw.bidx, rt.dst[0])) * D : nullptr;
+    __nv_bfloat16* const o_q1 = rt.dst[1] >= 0 ? out + static_cast<long long>(permuted_row32(sg, rw.bidx, rt.dst[1])) * D : nullptr;
+    const float nmr = -mu * rs;
+#pragma unroll
+    for (int k = 0; k < MAXV; ++k) {
+      if (k < nv) {
+        const int col = k * 128 + lane * 4;
+        const int quarter = col < D / 4 ? 0 : (col < D / 2 ? 1 : 2);
+        __nv_bfloat16* const dst = quarter == 0 ? o_q0 : (quarter == 1 ? o_q1 : o_self);
+        if (dst) {
+          const float4 ww = *reinterpret_cast<const float4*>(s_w + col), bb = *reinterpret_cast<const float4*>(s_b + col);
+          uint2 o;
+          o.x = pack_bf16x2(fmaf(fmaf(v[k].x, rs, nmr), ww.x, bb.x), fmaf(fmaf(v[k].y, rs, nmr), ww.y, bb.y));
+          o.y = pack_bf16x2(fmaf(fmaf(v[k].z, rs, nmr), ww.z, bb.z), fmaf(fmaf(v[k].w, rs, nmr), ww.w, bb.w));
+          *reinterpret_cast<uint2*>(dst + col) = o;
+        }
+        const bool z = quarter == 0 ? rt.zero[0] : (quarter == 1 ? rt.zero[1] : false);
+        if (z) *reinterpret_cast<uint2*>(o_self + col) = make_uint2(0u, 0u);   // nothing shifts into these channels
+      }
+    }
+    if (++slot == LNW_RING) { slot = 0; par ^= 1; }
   }
 }
 
@@ -600,8 +742,25 @@ extern "C" int b200_ln_shift_fwd(const float* x, const float* x2, const float* w
   ShiftGeom sg{seq, T, F, shift, row_split, M / seq};
   int blocks = num_sms() * 3;   // persistent: three 8-warp blocks per SM
   if (blocks * LNF_GROUPS > M) blocks = (M + LNF_GROUPS - 1) / LNF_GROUPS;
-  ln_shift_fwd_kernel<<<blocks, 128 * LNF_GROUPS, 0, st>>>(x, x2, w, b, reinterpret_cast<__nv_bfloat16*>(out), mean,
-                                                           rstd, M, D, eps, sg);
+  int ring_rows = 0;
+  size_t smem = 0;
+  if (!x2 && reinterpret_cast<uintptr_t>(x) % 16 == 0) {
+    const size_t wsmem = static_cast<size_t>(LNW_WARPS) * LNW_RING * D * 4 + LNW_WARPS * LNW_RING * 8 + 2 * D * 4;
+    static bool configured = false;
+    if (!configured) {
+      if (cudaFuncSetAttribute(ln_shift_fwd_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024) !=
+          cudaSuccess)
+        return -40;
+      configured = true;
+    }
+    int wblocks = num_sms() * 4;   // four 8-warp blocks per SM (the next row of a warp lands while it works on this one)
+    if (wblocks * LNW_WARPS > M) wblocks = (M + LNW_WARPS - 1) / LNW_WARPS;
+    ln_shift_fwd_warp_kernel<<<wblocks, 32 * LNW_WARPS, wsmem, st>>>(x, w, b, reinterpret_cast<__nv_bfloat16*>(out), mean,
+                                                                     rstd, M, D, eps, sg);
+    return err();
+  }
+  ln_shift_fwd_kernel<<<blocks, 128 * LNF_GROUPS, smem, st>>>(x, x2, w, b, reinterpret_cast<__nv_bfloat16*>(out), mean,
+                                                              rstd, M, D, eps, sg, ring_rows);
   return err();
 }
 

@@ -17,6 +17,19 @@ def timeit(fn, iters=30):
     return s.elapsed_time(e) / iters * 1e3  # us
 
 
+def timeit_graph(fn, iters=20):
+    """Device time per call: the calls are captured into one CUDA graph (no host launch cost between kernels)."""
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(iters): fn()
+    g.replay(); torch.cuda.synchronize()
+    s, e = torch.cuda.Event(True), torch.cuda.Event(True)
+    s.record(); g.replay(); e.record(); torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters * 1e3
+
+
 def box_speed():
     """cuBLAS bf16 8192^3 matmul TF/s: a yardstick for the box's current power/clock state."""
     a = torch.randn(8192, 8192, device='cuda', dtype=torch.bfloat16); b = torch.randn(8192, 8192, device='cuda', dtype=torch.bfloat16)
@@ -46,8 +59,10 @@ def main():
         print(f"attn {t}: fwd {f:.0f} us  bwd {b:.0f} us", flush=True)
     x = torch.randn(M, D, device=dev); w = torch.ones(D, device=dev); bb = torch.zeros(D, device=dev)
     h = torch.zeros(M, D, device=dev, dtype=torch.bfloat16); mean = torch.zeros(M, device=dev); rstd = torch.zeros(M, device=dev)
-    print(f"ln_shift_fwd {timeit(lambda: E.ln_shift_fwd(x, None, w, bb, h, mean, rstd, cfg, True)):.0f} us")
+    print(f"ln_shift_fwd {timeit(lambda: E.ln_shift_fwd(x, None, w, bb, h, mean, rstd, cfg, True)):.0f} us  (graph: {timeit_graph(lambda: E.ln_shift_fwd(x, None, w, bb, h, mean, rstd, cfg, True)):.0f} us)")
     dx = torch.zeros(M, D, device=dev); dw = torch.zeros(D, device=dev); db = torch.zeros(D, device=dev)
+    print(f"  (yardstick: torch fp32->bf16 cast of the same tensor, same bytes: {timeit_graph(lambda: h.copy_(x)):.0f} us; "
+          f"fp32 copy read+write 336 MB: {timeit_graph(lambda: dx.copy_(x)):.0f} us)")
     print(f"ln_shift_bwd {timeit(lambda: E.ln_shift_bwd(h, x, None, mean, rstd, w, dx, None, dw, db, cfg, True, 0)):.0f} us")
     o_n = torch.randn(M, D, device=dev).bfloat16(); d_on = torch.zeros(M, D, device=dev, dtype=torch.bfloat16)
     dsn = torch.zeros(D, device=dev); dbn = torch.zeros(D, device=dev)
