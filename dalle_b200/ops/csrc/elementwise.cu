@@ -367,12 +367,12 @@ struct LnBwdNext {
 };
 // Two row groups of 128 threads per block; three blocks per SM (<= 85 registers) without the tail, two (<= 128
 // registers) with it - sized so that neither variant spills.
-template <int LNB_GROUPS, bool TAIL>
+template <int LNB_GROUPS, bool TAIL, bool RING>
 __global__ void __launch_bounds__(128 * LNB_GROUPS, TAIL ? 2 : 3)
 ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restrict__ x, const float* __restrict__ x2,
                     const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ w,
                     float* __restrict__ dx_out, float* __restrict__ dx2_out, float* __restrict__ dw,
-                    float* __restrict__ db, int M, int D, ShiftGeom sg, int mode, LnBwdNext nx) {
+                    float* __restrict__ db, int M, int D, ShiftGeom sg, int mode, LnBwdNext nx, int ring_rows) {
   __shared__ float sred[LNB_GROUPS][2][4][2];   // [group][parity][warp][s1, s2]
   __shared__ float s_acc[LNB_GROUPS - 1][2][128 * MAXV];
   const int grp = threadIdx.x >> 7;            // row group of the block
@@ -400,8 +400,43 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
   const int groups_total = gridDim.x * LNB_GROUPS;
   const int rows_per = (M + groups_total - 1) / groups_total;   // every row group owns a contiguous range of rows
   const int row_begin = min(M, (blockIdx.x * LNB_GROUPS + grp) * rows_per), row_end = min(M, row_begin + rows_per);
-  RowWalk rw;
+  // Optional shared-memory ring (mode 0): a row's inputs - x, the old dx, the three shifted pieces of dh, the tail's o -
+  // arrive by bulk async copies `ring_rows` rows ahead; the bytes in flight then cost no registers and more blocks
+  // fit on an SM.  Slot layout: [x : 4D][dx : 4D][dh : 2D][o : 2D] bytes.
+  extern __shared__ __align__(128) uint8_t ring_raw[];
+  const size_t slot_bytes = static_cast<size_t>(D) * (TAIL ? 12 : 10);
+  uint8_t* ring = ring_raw + static_cast<size_t>(grp) * ring_rows * slot_bytes;
+  uint64_t* rbar = reinterpret_cast<uint64_t*>(ring_raw + static_cast<size_t>(LNB_GROUPS) * ring_rows * slot_bytes) +
+                   grp * ring_rows;
+  auto issue_row = [&](const RowWalk& w_, int slot) {   // one thread of the group
+    const ShiftRoute rt_ = shift_route(sg, w_);
+    uint8_t* dst = ring + slot * slot_bytes;
+    const __nv_bfloat16* p_self = dh + static_cast<long long>(permuted_row32(sg, w_.bidx, w_.t)) * D;
+    const uint32_t nq = (rt_.dst[0] >= 0 ? 1u : 0u) + (rt_.dst[1] >= 0 ? 1u : 0u);
+    mbar_expect_tx(&rbar[slot], static_cast<uint32_t>(D) * (TAIL ? 11u : 9u) + nq * (D / 2));
+    bulk_copy_g2s(dst, x + static_cast<long long>(w_.row) * D, D * 4, &rbar[slot]);
+    bulk_copy_g2s(dst + D * 4, dx_out + static_cast<long long>(w_.row) * D, D * 4, &rbar[slot]);
+    if (rt_.dst[0] >= 0)
+      bulk_copy_g2s(dst + D * 8, dh + static_cast<long long>(permuted_row32(sg, w_.bidx, rt_.dst[0])) * D, D / 2, &rbar[slot]);
+    if (rt_.dst[1] >= 0)
+      bulk_copy_g2s(dst + D * 8 + D / 2, dh + static_cast<long long>(permuted_row32(sg, w_.bidx, rt_.dst[1])) * D + D / 4,
+                    D / 2, &rbar[slot]);
+    bulk_copy_g2s(dst + D * 9, p_self + D / 2, D, &rbar[slot]);
+    if (TAIL) bulk_copy_g2s(dst + D * 10, nx.o + static_cast<long long>(w_.row) * D, D * 2, &rbar[slot]);
+  };
+  RowWalk rw, rl;
   rw.init(sg, row_begin);
+  rl = rw;
+  int slot = 0;
+  uint32_t rpar = 0;
+  if (RING) {
+    if (t128 == 0) {
+      for (int s_ = 0; s_ < ring_rows; ++s_) mbar_init(&rbar[s_], 1);
+      fence_barrier_init();
+      for (int s_ = 0; s_ < ring_rows && rl.row < row_end; ++s_, rl.next(sg)) issue_row(rl, s_);
+    }
+    asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+  }
   for (int it = 0; rw.row < row_end; rw.next(sg), ++it) {
     const int row = rw.row;
     const ShiftRoute rt = shift_route(sg, rw);
@@ -415,7 +450,16 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
     for (int k = 0; k < 2; ++k) {
       u[k] = uo[k] = make_uint2(0u, 0u);
       v[k] = v2[k] = old[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (act[k]) {
+      if (act[k] && RING) {
+        if (k == 0) mbar_wait(&rbar[slot], rpar);
+        const int col = colk[k];
+        const uint8_t* sl = ring + slot * slot_bytes;
+        const long long src = col < D / 4 ? r_q0 : (col < D / 2 ? r_q1 : r_self);
+        if (src >= 0) u[k] = *reinterpret_cast<const uint2*>(sl + D * 8 + col * 2);
+        v[k] = *reinterpret_cast<const float4*>(sl + col * 4);
+        old[k] = *reinterpret_cast<const float4*>(sl + D * 4 + col * 4);
+        if (TAIL) uo[k] = *reinterpret_cast<const uint2*>(sl + D * 10 + col * 2);
+      } else if (act[k]) {
         const int col = colk[k];
         const long long src = col < D / 4 ? r_q0 : (col < D / 2 ? r_q1 : r_self);
         if (src >= 0) u[k] = *reinterpret_cast<const uint2*>(dh + src + col);
@@ -446,6 +490,10 @@ ln_shift_bwd_kernel(const __nv_bfloat16* __restrict__ dh, const float* __restric
     float* red = &sred[grp][it & 1][0][0];
     if ((threadIdx.x & 31) == 0) { red[wsub * 2] = s1; red[wsub * 2 + 1] = s2; }
     asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");   // the row group's own barrier
+    if (RING) {   // every thread of the group holds this row in registers: refill its slot
+      if (t128 == 0 && rl.row < row_end) { issue_row(rl, slot); rl.next(sg); }
+      if (++slot == ring_rows) { slot = 0; rpar ^= 1; }
+    }
     s1 = (red[0] + red[2] + red[4] + red[6]) / D;
     s2 = (red[1] + red[3] + red[5] + red[7]) / D;
 #pragma unroll
@@ -773,14 +821,31 @@ static int ln_shift_bwd_launch(const void* dh, const float* x, const float* x2, 
   if (D % 512 && D != 256) return -41;  // 4 warps per row: D in {256, 512, 1024}
   if (nx.o && mode != 0) return -41;
   const __nv_bfloat16* dhp = reinterpret_cast<const __nv_bfloat16*>(dh);
-  if (nx.o) {
-    int blocks = num_sms() * 2;   // persistent: two 8-warp blocks per SM (no register spills with the tail)
+  const bool ring_ok = mode == 0 && !x2 && D % 64 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 &&
+                       reinterpret_cast<uintptr_t>(dx) % 16 == 0 && reinterpret_cast<uintptr_t>(dh) % 16 == 0 &&
+                       (!nx.o || reinterpret_cast<uintptr_t>(nx.o) % 16 == 0);
+  const int ring_rows = 2;
+  const size_t ring_smem = 2 * (static_cast<size_t>(ring_rows) * D * (nx.o ? 12 : 10) + ring_rows * 8);
+  int blocks = num_sms() * 3;   // persistent: three 8-warp blocks per SM
+  if (blocks * 2 > M) blocks = (M + 1) / 2;
+  if (ring_ok && ring_smem <= 80 * 1024) {
+    static bool configured = false;
+    if (!configured) {
+      cudaFuncSetAttribute(ln_shift_bwd_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+      cudaFuncSetAttribute(ln_shift_bwd_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+      configured = true;
+    }
+    if (nx.o && blocks > num_sms() * 2) blocks = num_sms() * 2;   // (register-limited to two blocks per SM)
+    if (nx.o)
+      ln_shift_bwd_kernel<2, true, true><<<blocks, 256, ring_smem, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx, ring_rows);
+    else
+      ln_shift_bwd_kernel<2, false, true><<<blocks, 256, ring_smem, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx, ring_rows);
+  } else if (nx.o) {
+    blocks = num_sms() * 2;   // two 8-warp blocks per SM (no register spills with the tail)
     if (blocks * 2 > M) blocks = (M + 1) / 2;
-    ln_shift_bwd_kernel<2, true><<<blocks, 256, 0, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx);
+    ln_shift_bwd_kernel<2, true, false><<<blocks, 256, 0, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx, 0);
   } else {
-    int blocks = num_sms() * 3;   // persistent: three 8-warp blocks per SM
-    if (blocks * 2 > M) blocks = (M + 1) / 2;
-    ln_shift_bwd_kernel<2, false><<<blocks, 256, 0, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx);
+    ln_shift_bwd_kernel<2, false, false><<<blocks, 256, 0, st>>>(dhp, x, x2, mean, rstd, w, dx, dx2, dw, db, M, D, sg, mode, nx, 0);
   }
   return err();
 }
