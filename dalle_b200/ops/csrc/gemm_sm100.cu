@@ -19,6 +19,9 @@
 
 namespace b200 {
 
+// internal variant of B200_EPI_RESID for long reductions (K >= 2048): a fourth mainloop stage instead of a second
+// staging set, bf16 side output by plain row stores
+constexpr int EPI_RESID_DEEP = 7;
 constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;
@@ -29,7 +32,7 @@ constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64
 constexpr int OUT_TILES_PER_WARP = 3;
 constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
 __host__ __device__ constexpr int gemm_stages(int epi) {
-  return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;
+  return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;   // (RESID_DEEP: 4)
 }
 // Epilogue warps per CTA: 4 per TMEM lane quarter x column parts.  (16 warps were measured on the GEGLU backward
 // epilogue: no gain.  An ablation showed why: that kernel's time is its 1.3 GB of epilogue loads + stores, whose
@@ -211,7 +214,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 32 * gemm_epi_warps(EPI));
     }
-    if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == B200_EPI_ATOMIC_F32)
+    if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP || EPI == B200_EPI_ATOMIC_F32)
       for (int s = 0; s < 2 * gemm_epi_warps(EPI); ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
@@ -413,11 +416,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_expect_tx(&my_aux_bar[set], 2 * OUT_TILE_BYTES);
       tma_load_2d(stage + (2 * set) * OUT_TILE_BYTES, &tmX, &my_aux_bar[set], x, y);
     };
-    if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID) && blockIdx.x < g.m_tiles * g.n_tiles && lane == 0) {
+    if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) && blockIdx.x < g.m_tiles * g.n_tiles && lane == 0) {
       const int t0 = blockIdx.x;   // (these epilogues never split K)
       const int x0 = (t0 % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
       if (x0 < g.N) {
-        if (EPI == B200_EPI_RESID) res_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
+        if (EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) res_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
         else aux_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
       }
     }
@@ -534,6 +537,60 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           stage_flush(&tmO, 2 * set + 1, g.n_half + col, y);
           stage_commit();
           if (NSETS == 1) prefetch_next(ci, col);
+        }
+      } else if (EPI == EPI_RESID_DEEP) {
+        // One staging set per warp (a fourth mainloop stage is worth more than a second set: measured): the next
+        // chunk's tile is requested as soon as this chunk's store has read the buffer.  The bf16 copy of
+        // (acc + bias) goes out with plain row stores.
+        const int y = m_blk * BM + q * 32;
+#pragma unroll 1
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c = cpart * NCH + ci;
+          const int col = n0 + c * 32;
+          if (col >= g.N) continue;  // warp-uniform (never prefetched either)
+          mbar_wait(&my_aux_bar[0], aux_n & 1);
+          ++aux_n;
+          uint32_t r[32];
+          tmem_ld32(taddr + c * 32, r);
+          tmem_ld_wait();
+          uint8_t* trow_ = stage + lane * 128;
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 sc = make_float4(0.f, 0.f, 0.f, 0.f), bb = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (col + j < g.N) {   // N % 4 == 0 (checked by the host)
+              sc = __ldg(reinterpret_cast<const float4*>(g.scale + col + j));
+              if (g.bias) bb = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
+            }
+            float4* cell = reinterpret_cast<float4*>(trow_ + ((((j >> 2) ^ (lane & 7))) << 4));
+            const float4 rr = *cell;
+            v[j] = __uint_as_float(r[j]) + bb.x;
+            v[j + 1] = __uint_as_float(r[j + 1]) + bb.y;
+            v[j + 2] = __uint_as_float(r[j + 2]) + bb.z;
+            v[j + 3] = __uint_as_float(r[j + 3]) + bb.w;
+            *cell = make_float4(rr.x + g.alpha * sc.x * v[j], rr.y + g.alpha * sc.y * v[j + 1],
+                                rr.z + g.alpha * sc.z * v[j + 2], rr.w + g.alpha * sc.w * v[j + 3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          stage_flush(&tmO, 0, col, y);
+          stage_commit();
+          if (g.out2 && row_ok)
+            store_row_bf16(reinterpret_cast<__nv_bfloat16*>(g.out2) + (long long)row * g.ldo2, col, g.N, v);
+          {   // request the next chunk's residual tile (of this tile, or the first of the CTA's next tile)
+            int ncol = col + 32, ny = y;
+            bool have = ci + 1 < NCH && ncol < g.N;   // (chunks past N are skipped, so look beyond them)
+            if (!have) {
+              GemmUnit nx;
+              have = gemm_unit(g, ui + 1, nx);
+              ncol = (nx.t % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
+              ny = (nx.t / g.n_tiles) * BM + q * 32;
+            }
+            if (have && ncol < g.N) {
+              stage_reuse();
+              if (lane == 0) res_load(0, ncol, ny);
+            }
+          }
         }
       } else if (EPI == B200_EPI_RESID) {
         // out = res + alpha * scale[col] * (acc + bias[col]); optional bf16 copy of (acc + bias).
@@ -921,7 +978,9 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   if (d->mode == B200_GEMM_NT) {
     switch (d->epi) {
       case B200_EPI_ROTARY: return launch<0, 0, B200_EPI_ROTARY>(ta, tb, g, grid, st);
-      case B200_EPI_RESID: return launch<0, 0, B200_EPI_RESID>(ta, tb, g, grid, st);
+      case B200_EPI_RESID:
+        if (d->K >= 2048) return launch<0, 0, EPI_RESID_DEEP>(ta, tb, g, grid, st);
+        return launch<0, 0, B200_EPI_RESID>(ta, tb, g, grid, st);
       case B200_EPI_GEGLU: return launch<0, 0, B200_EPI_GEGLU>(ta, tb, g, grid, st);
       default: break;
     }

@@ -50,8 +50,8 @@ def test_tn_wgrad_accumulates(M, N, K):
     _check(out.cpu(), ref, tol=5e-3)
 
 
-def test_resid_epilogue():
-    M, N, K = 512, 1024, 1024
+@pytest.mark.parametrize("M,N,K", [(512, 1024, 1024), (384, 1000, 2048), (200, 64, 4096)])   # K >= 2048: deep variant
+def test_resid_epilogue(M, N, K):
     A, B = _rand(M, K), _rand(N, K, scale=0.05)
     bias, scale = torch.randn(N, device="cuda"), torch.rand(N, device="cuda")
     res = torch.randn(M, N, device="cuda")
