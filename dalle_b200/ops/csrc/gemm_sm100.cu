@@ -32,7 +32,7 @@ constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64
 constexpr int OUT_TILES_PER_WARP = 3;
 constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
 __host__ __device__ constexpr int gemm_stages(int epi) {
-  return (epi == B200_EPI_GEGLU || epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;   // (RESID_DEEP: 4)
+  return (epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;   // (RESID_DEEP: 4)
 }
 // Epilogue warps per CTA: 4 per TMEM lane quarter x column parts.  (16 warps were measured on the GEGLU backward
 // epilogue: no gain.  An ablation showed why: that kernel's time is its 1.3 GB of epilogue loads + stores, whose
@@ -44,7 +44,7 @@ __host__ __device__ constexpr int gemm_threads(int epi) {
   return 64 + 32 * gemm_epi_warps(epi) + 32 * gemm_sum_warps(epi);
 }
 __host__ __device__ constexpr int gemm_out_tiles(int epi) {   // staging tiles per epilogue warp
-  return epi == B200_EPI_GEGLU ? 3 : (epi == B200_EPI_GEGLU_BWD ? (gemm_epi_warps(epi) == 16 ? 2 : 4) : (epi == B200_EPI_RESID ? 5 : 2));
+  return epi == B200_EPI_GEGLU ? 2 : (epi == B200_EPI_GEGLU_BWD ? (gemm_epi_warps(epi) == 16 ? 2 : 4) : (epi == B200_EPI_RESID ? 5 : 2));
 }
 __host__ __device__ constexpr int gemm_out_stage_bytes(int epi) {
   return gemm_epi_warps(epi) * gemm_out_tiles(epi) * OUT_TILE_BYTES;
@@ -404,6 +404,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     auto stage_commit = [&]() {
       if (lane == 0) tma_store_commit();
     };
+    uint32_t ring_n = 0;
+    auto ring_store = [&](const CUtensorMap* m, const float* v32, int x, int y) {
+      const int tile = ring_n % TILES;
+      ++ring_n;
+      if (lane == 0) tma_store_wait_read_pending<(TILES > 1 ? TILES - 1 : 0)>();
+      __syncwarp();
+      stage_write(tile, v32);
+      fence_proxy_async_smem();
+      __syncwarp();
+      stage_flush(m, tile, x, y);
+      stage_commit();
+    };
     uint64_t* my_aux_bar = aux_bar + (warp - 2) * 2;
     uint32_t aux_n = 0;   // chunks consumed so far: set = aux_n & 1, mbarrier parity = (aux_n >> 1) & 1
     auto aux_load = [&](int set, int x, int y) {   // one lane: both aux tiles of a chunk -> staging set
@@ -462,14 +474,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               o[j] = o2.x; o[j + 1] = o2.y;
             }
             const int y = m_blk * BM + q * 32;
-            stage_reuse();
-            stage_write(0, o);
-            if (g.out2) { stage_write(1, va); stage_write(2, vg); }
-            fence_proxy_async_smem();
-            __syncwarp();
-            stage_flush(&tmO, 0, col, y);
-            if (g.out2) { stage_flush(&tmO2, 1, col, y); stage_flush(&tmO2, 2, g.n_half + col, y); }
-            stage_commit();
+            // the warp's staging tiles form a ring with one commit group per store: a tile is rewritten as soon as
+            // the store issued TILES stores ago has read it
+            ring_store(&tmO, o, col, y);
+            if (g.out2) {
+              ring_store(&tmO2, va, col, y);
+              ring_store(&tmO2, vg, g.n_half + col, y);
+            }
           }
         }
       } else if (EPI == B200_EPI_GEGLU_BWD) {

@@ -8,6 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import pathlib
 from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
@@ -70,6 +71,9 @@ def cuda_lib() -> ctypes.CDLL:
     global _cuda
     if _cuda is None:
         path = _HERE / "libdalle_b200.so"
+        alt = os.environ.get("DALLE_B200_LIB")   # developer switch: A/B two builds inside one benchmark job
+        if alt:
+            path = pathlib.Path(alt)
         if not path.exists():
             _try_build()
         if not path.exists():
