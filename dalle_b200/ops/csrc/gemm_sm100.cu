@@ -685,12 +685,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] *= g.alpha;
             }
-            stage_reuse();
-            stage_write(0, v);
-            fence_proxy_async_smem();
-            __syncwarp();
-            stage_flush(&tmO, 0, col, y);
-            stage_commit();
+            ring_store(&tmO, v, col, y);   // two staging tiles: one store stays in flight behind the next chunk
           } else if (EPI == B200_EPI_ROTARY) {
             // interleaved-pair rotary on q, k and v; q additionally scaled (dalle-pytorch applies
             // rotary to v as well)
@@ -706,12 +701,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
               o[j] = (x0 * cs.x - x1 * cs.y) * s;
               o[j + 1] = (x1 * cs.x + x0 * cs.y) * s;
             }
-            stage_reuse();
-            stage_write(0, o);
-            fence_proxy_async_smem();
-            __syncwarp();
-            stage_flush(&tmO, 0, col, y);
-            stage_commit();
+            ring_store(&tmO, o, col, y);
           } else if (EPI == B200_EPI_ATOMIC_F32) {
             float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
             if (full) {
