@@ -60,12 +60,18 @@ class GroupTrainer:
 
             self.group = FusedGroupAverager(self.opt, process_group)
         self.steps = 0
+        from .utils.phases import PhaseTrace
+
+        self.trace = PhaseTrace()   # NVTX ranges + device-timed phases when DALLE_B200_TRACE=1
 
     # ---- one optimisation step on device-resident inputs -----------------------------------------
     def step(self, text: torch.Tensor, image: torch.Tensor) -> torch.Tensor:
-        loss = self.model(text, image, return_loss=True)
-        loss.backward()
-        self.optimizer_step()
+        with self.trace.phase("forward"):
+            loss = self.model(text, image, return_loss=True)
+        with self.trace.phase("backward"):
+            loss.backward()
+        with self.trace.phase("averaging+optimizer"):
+            self.optimizer_step()
         return loss.detach()
 
     def accumulate(self, text, image) -> torch.Tensor:

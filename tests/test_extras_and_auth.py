@@ -137,3 +137,19 @@ def test_allreduce_survives_a_peer_that_dies_midway(monkeypatch):
     finally:
         for d in (d0, d1, d2):
             d.shutdown()
+
+
+def test_phase_trace_is_inert_without_cuda_and_times_with_it():
+    """phase tracing (NVTX + CUDA events) must be free when off and never change results."""
+    import torch
+    from dalle_b200.utils.phases import PhaseTrace
+
+    t = PhaseTrace(enabled=True)
+    with t.phase("forward"):
+        x = torch.ones(4).sum()
+    assert x.item() == 4.0
+    s = t.summary()
+    if torch.cuda.is_available():
+        assert "forward" in s and s["forward"] >= 0.0
+    else:
+        assert s == {}
