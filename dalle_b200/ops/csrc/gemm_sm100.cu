@@ -445,7 +445,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * g.tile_n_step;
       const bool row_ok = row < g.M;
-      mbar_wait(&tfull_bar[acc], acc_phase);
+      // the accumulator wait spans most of a mainloop: one sleeping poller per warp instead of 32 spinning lanes
+      // (issue slots and power go to the MMA / TMA threads)
+      if (lane == 0) mbar_wait_backoff(&tfull_bar[acc], acc_phase, 64);
+      __syncwarp();
       tc_fence_after();
       const uint32_t taddr = tmem_base + acc * BN + (static_cast<uint32_t>(q * 32) << 16);
 
