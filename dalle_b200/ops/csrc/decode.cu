@@ -259,43 +259,88 @@ decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, fl
   const float mx = val(0);
   int keep = n;
   if (top_k > 0 && top_k < keep) keep = top_k;
-  // total mass of the kept prefix (needed for the nucleus cut as well)
-  float s = 0.f;
-  for (int i = tid; i < keep; i += blockDim.x) s += __expf(val(i) - mx);  // mass after the top-k cut
-  s = warp_sum(s);
-  if ((tid & 31) == 0) sred[tid >> 5] = s;
+  // Block-parallel nucleus cut and draw over the sorted row (a single-thread walk costs > 1 ms when the
+  // distribution is flat and the nucleus holds thousands of tokens): every thread owns `per` consecutive ranks.
+  __shared__ float swarp[32];
+  __shared__ int smin[2];
+  const int per = (npow + blockDim.x - 1) / blockDim.x;   // <= 8
+  const int i0 = tid * per;
+  float e[8];
+  float local = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int i = i0 + k;
+    e[k] = (k < per && i < keep) ? __expf(val(i) - mx) : 0.f;
+    local += e[k];
+  }
+  // exclusive scan of the per-thread sums over the block
+  auto block_exclusive = [&](float v, float& total_out) -> float {
+    const int lane = tid & 31, w = tid >> 5;
+    float inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const float t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    __syncthreads();                 // (swarp reuse between calls)
+    if (lane == 31) swarp[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+      float x = lane < (blockDim.x >> 5) ? swarp[lane] : 0.f;
+      float xi = x;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float t = __shfl_up_sync(0xffffffffu, xi, o);
+        if (lane >= o) xi += t;
+      }
+      swarp[lane] = xi - x;          // exclusive warp offsets
+      if (lane == 31) sbc[0] = xi;   // block total
+    }
+    __syncthreads();
+    total_out = sbc[0];
+    return swarp[w] + inc - v;
+  };
+  float total;
+  const float off = block_exclusive(local, total);
+  if (tid == 0) { smin[0] = keep; smin[1] = 0x7fffffff; }
   __syncthreads();
-  if (tid == 0) {
-    float t = 0.f;
-    for (int i = 0; i < (blockDim.x >> 5); ++i) t += sred[i];
-    sbc[0] = t;
+  if (top_p < 1.0f) {
+    // keep tokens while the mass BEFORE them is <= top_p: the cut is the first rank whose preceding mass exceeds it
+    float cum = off;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int i = i0 + k;
+      if (k < per && i < keep && cum / total > top_p) { atomicMin(&smin[0], i); break; }
+      cum += e[k];
+    }
   }
   __syncthreads();
-  const float total = sbc[0];
-  if (tid == 0) {
-    // sequential walk over the sorted prefix: cheap (the nucleus is short) and exact
-    float cum = 0.f;
-    int cut = keep;
-    if (top_p < 1.0f) {
-      for (int i = 0; i < keep; ++i) {
-        const float p = __expf(val(i) - mx) / total;
-        if (cum > top_p) { cut = i; break; }  // keep tokens while the mass BEFORE them is <= top_p
-        cum += p;
+  const int cut = max(smin[0], 1);
+  // mass of the kept prefix, then the draw
+  float kl = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (k < per && i0 + k < cut) kl += e[k];
+  float kept;
+  const float koff = block_exclusive(kl, kept);
+  const unsigned long long seed = *seed_ptr;
+  const uint32_t r = hash_u32(static_cast<uint32_t>(seed) ^ hash_u32(static_cast<uint32_t>(seed >> 32) + 0x9e3779b9u * (pos + 1)) ^
+                              hash_u32(0x85ebca6bu * (b + 1)));
+  const float u = (static_cast<float>(r >> 8) + 0.5f) * (1.0f / 16777216.0f) * kept;
+  {
+    float acc = koff;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int i = i0 + k;
+      if (k < per && i < cut) {
+        acc += e[k];
+        if (acc >= u) { atomicMin(&smin[1], i); break; }
       }
-      if (cut < 1) cut = 1;
     }
-    float kept = 0.f;
-    for (int i = 0; i < cut; ++i) kept += __expf(val(i) - mx);
-    const unsigned long long seed = *seed_ptr;
-    const uint32_t r = hash_u32(static_cast<uint32_t>(seed) ^ hash_u32(static_cast<uint32_t>(seed >> 32) + 0x9e3779b9u * (pos + 1)) ^
-                                hash_u32(0x85ebca6bu * (b + 1)));
-    const float u = (static_cast<float>(r >> 8) + 0.5f) * (1.0f / 16777216.0f) * kept;
-    float acc = 0.f;
-    int pick = cut - 1;
-    for (int i = 0; i < cut; ++i) {
-      acc += __expf(val(i) - mx);
-      if (acc >= u) { pick = i; break; }
-    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    const int pick = smin[1] == 0x7fffffff ? cut - 1 : smin[1];
     const long long tok = 0xffffffffu - static_cast<uint32_t>(skeys[pick] & 0xffffffffu);
     ids[static_cast<long long>(b) * ids_stride + pos + 1] = tok + id_offset;
     if (pos + 1 - T >= 0) codes[static_cast<long long>(b) * codes_stride + (pos + 1 - T)] = tok;
