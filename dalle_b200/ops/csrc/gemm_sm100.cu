@@ -707,6 +707,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             ring_store(&tmO, o, col, y);
           } else if (EPI == B200_EPI_ATOMIC_F32) {
             float* op = reinterpret_cast<float*>(g.out) + (long long)row * g.ldo + col;
+            if (g.scale) {
+              // split-K form of the in-place residual epilogue (few-row GEMMs of the decode path):
+              // out += alpha * scale[col] * (partial + bias[col] in the first split)
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (col + j < g.N) {
+                  const float bj = (g.bias && un.kb0 == 0) ? __ldg(g.bias + col + j) : 0.f;
+                  v[j] = __ldg(g.scale + col + j) * (v[j] + bj);
+                } else {
+                  v[j] = 0.f;
+                }
+              }
+            }
             if (full) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4)
@@ -856,8 +869,15 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g
 
 using namespace b200;
 
-extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
-  if (d->M <= 0 || d->N <= 0 || d->K <= 0) return 0;
+extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
+  if (d_in->M <= 0 || d_in->N <= 0 || d_in->K <= 0) return 0;
+  B200Gemm dd = *d_in;
+  const B200Gemm* d = &dd;
+  // Few-row in-place residual GEMMs (decode: M = batch) have only N / 256 output tiles: run them split-K through the
+  // accumulating epilogue, which applies LayerScale and adds the bias in the first split.
+  const bool resid_atomic = dd.epi == B200_EPI_RESID && dd.mode == B200_GEMM_NT && dd.M <= BM && dd.K >= 2048 &&
+                            dd.res == dd.out && dd.out2 == nullptr && dd.ldres == dd.ldo;
+  if (resid_atomic) { dd.epi = B200_EPI_ATOMIC_F32; dd.splits = 0; }
   const int a_mn = (d->mode == B200_GEMM_TN) ? 1 : 0;
   const int b_mn = (d->mode == B200_GEMM_NT) ? 0 : 1;
   if ((d->lda % 8) || (d->ldb % 8)) return -10;  // TMA needs 16-byte row strides
@@ -897,7 +917,8 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
       // (an equal-share stream-K cut of the k-block space measured 1.5x SLOWER here: CTAs at unrelated K
       // offsets lose the L2 reuse of the A / B panels that lock-step units share)
       const int sms = num_sms();
-      const int max_splits = g.kb_total / 32 > 0 ? (g.kb_total / 32 < 16 ? g.kb_total / 32 : 16) : 1;
+      const int min_kb = resid_atomic ? 8 : 32;   // k-blocks per unit
+      const int max_splits = g.kb_total / min_kb > 0 ? (g.kb_total / min_kb < 16 ? g.kb_total / min_kb : 16) : 1;
       float best = -1.f;
       for (int sp = 1; sp <= max_splits; ++sp) {
         const int units = tiles * sp;
@@ -927,6 +948,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d, void* stream) {
   g.n_half = d->n_half;
   g.alpha = d->alpha;
   if (d->a_colsum && !(a_mn && d->epi == B200_EPI_ATOMIC_F32)) return -16;
+  if (d->epi == B200_EPI_ATOMIC_F32 && !resid_atomic) g.scale = nullptr;
   g.a_colsum = d->a_colsum;
 
   // output maps for the TMA-store epilogues

@@ -109,3 +109,15 @@ def test_wgrad_with_fused_bias_gradient():
     _check(out.cpu(), A.float().cpu().t() @ B.float().cpu(), tol=5e-3)
     ref = 0.5 + A.float().sum(0).cpu()
     assert (cs.cpu() - ref).abs().max().item() < 2e-3 * ref.abs().max().item() + 1e-3
+
+
+def test_resid_few_rows_in_place_split_k():
+    """Decode-shaped residual GEMM (M = batch rows, in place): takes the split-K accumulate path."""
+    M, N, K = 32, 1024, 4096
+    A, B = _rand(M, K), _rand(N, K, scale=0.03)
+    bias, scale = torch.randn(N, device="cuda"), torch.rand(N, device="cuda")
+    x = torch.randn(M, N, device="cuda")
+    ref = torch.empty(M, N)
+    G.gemm_ref(G.NT, G.EPI_RESID, A.cpu(), B.cpu(), ref, bias=bias.cpu(), scale=scale.cpu(), res=x.cpu().clone(), alpha=1.0)
+    G.gemm(G.NT, G.EPI_RESID, A, B, x, bias=bias, scale=scale, res=x, alpha=1.0)
+    _check(x.cpu(), ref, tol=1e-3)
