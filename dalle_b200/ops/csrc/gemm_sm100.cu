@@ -875,7 +875,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
   const B200Gemm* d = &dd;
   // Few-row in-place residual GEMMs (decode: M = batch) have only N / 256 output tiles: run them split-K through the
   // accumulating epilogue, which applies LayerScale and adds the bias in the first split.
-  const bool resid_atomic = dd.epi == B200_EPI_RESID && dd.mode == B200_GEMM_NT && dd.M <= BM && dd.K >= 2048 &&
+  const bool resid_atomic = dd.epi == B200_EPI_RESID && dd.mode == B200_GEMM_NT && dd.M <= BM && dd.K >= 1024 &&
                             dd.res == dd.out && dd.out2 == nullptr && dd.ldres == dd.ldo;
   if (resid_atomic) { dd.epi = B200_EPI_ATOMIC_F32; dd.splits = 0; }
   const int a_mn = (d->mode == B200_GEMM_TN) ? 1 : 0;
@@ -917,7 +917,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
       // (an equal-share stream-K cut of the k-block space measured 1.5x SLOWER here: CTAs at unrelated K
       // offsets lose the L2 reuse of the A / B panels that lock-step units share)
       const int sms = num_sms();
-      const int min_kb = resid_atomic ? 8 : 32;   // k-blocks per unit
+      const int min_kb = resid_atomic ? 4 : 32;   // k-blocks per unit
       const int max_splits = g.kb_total / min_kb > 0 ? (g.kb_total / min_kb < 16 ? g.kb_total / min_kb : 16) : 1;
       float best = -1.f;
       for (int sp = 1; sp <= max_splits; ++sp) {
