@@ -42,16 +42,38 @@ __global__ void decode_ln_shift_kernel(const float* __restrict__ x, const float*
   if (b >= g.B) return;
   const int pos = *pos_ptr, D = g.D;
   const int nv = D / 128;
-  float4 v[8];
+  // which earlier positions feed the shifted channels
+  int src_a = -1, src_b = -1;  // source position for channels [0, D/4) and [D/4, D/2)
+  if (shift) {
+    if (pos < g.T) {
+      src_a = src_b = pos >= 1 ? pos - 1 : -1;
+    } else {
+      const int p = pos - g.T, r = p / g.F, c = p - r * g.F;
+      src_a = r >= 1 ? pos - g.F : -1;
+      src_b = c >= 1 ? pos - 1 : -1;
+    }
+  }
+  // every load that does not depend on the statistics is issued up front (the kernel is one short latency chain)
+  float4 v[8], ww[8], bb[8];
+  uint2 cached[8];
   float s = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     if (k < nv) {
-      const long long off = static_cast<long long>(b) * D + k * 128 + lane * 4;
+      const int col = k * 128 + lane * 4;
+      const long long off = static_cast<long long>(b) * D + col;
       v[k] = *reinterpret_cast<const float4*>(x + off);
       if (x2) {
         const float4 u = *reinterpret_cast<const float4*>(x2 + off);
         v[k] = make_float4(0.5f * (v[k].x + u.x), 0.5f * (v[k].y + u.y), 0.5f * (v[k].z + u.z), 0.5f * (v[k].w + u.w));
+      }
+      ww[k] = __ldg(reinterpret_cast<const float4*>(w + col));
+      bb[k] = __ldg(reinterpret_cast<const float4*>(bias + col));
+      cached[k] = make_uint2(0u, 0u);
+      if (shift && col < D / 2) {
+        const int src = col < D / 4 ? src_a : src_b;
+        if (src >= 0)
+          cached[k] = *reinterpret_cast<const uint2*>(cache + (static_cast<long long>(b) * g.seq + src) * (D / 2) + col);
       }
       s += v[k].x + v[k].y + v[k].z + v[k].w;
     }
@@ -65,34 +87,17 @@ __global__ void decode_ln_shift_kernel(const float* __restrict__ x, const float*
       q += a * a + c * c + d * d + e * e;
     }
   const float rs = rsqrtf(warp_sum(q) / D + eps);
-  // which earlier positions feed the shifted channels
-  int src_a = -1, src_b = -1;  // source position for channels [0, D/4) and [D/4, D/2)
-  if (shift) {
-    if (pos < g.T) {
-      src_a = src_b = pos >= 1 ? pos - 1 : -1;
-    } else {
-      const int p = pos - g.T, r = p / g.F, c = p - r * g.F;
-      src_a = r >= 1 ? pos - g.F : -1;
-      src_b = c >= 1 ? pos - 1 : -1;
-    }
-  }
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     if (k < nv) {
       const int col = k * 128 + lane * 4;
-      const float4 ww = __ldg(reinterpret_cast<const float4*>(w + col));
-      const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + col));
       uint2 o;
-      o.x = pack_bf16x2((v[k].x - mu) * rs * ww.x + bb.x, (v[k].y - mu) * rs * ww.y + bb.y);
-      o.y = pack_bf16x2((v[k].z - mu) * rs * ww.z + bb.z, (v[k].w - mu) * rs * ww.w + bb.w);
+      o.x = pack_bf16x2((v[k].x - mu) * rs * ww[k].x + bb[k].x, (v[k].y - mu) * rs * ww[k].y + bb[k].y);
+      o.y = pack_bf16x2((v[k].z - mu) * rs * ww[k].z + bb[k].z, (v[k].w - mu) * rs * ww[k].w + bb[k].w);
       if (shift && col < D / 2) {
         __nv_bfloat16* crow = cache + (static_cast<long long>(b) * g.seq + pos) * (D / 2) + col;
         *reinterpret_cast<uint2*>(crow) = o;  // remember this token's own normalised half for later positions
-        const int src = col < D / 4 ? src_a : src_b;
-        if (src >= 0)
-          o = *reinterpret_cast<const uint2*>(cache + (static_cast<long long>(b) * g.seq + src) * (D / 2) + col);
-        else
-          o = make_uint2(0u, 0u);
+        o = cached[k];
       }
       *reinterpret_cast<uint2*>(out + static_cast<long long>(b) * D + col) = o;
     }
