@@ -160,12 +160,16 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
 
   // ---- phase 1: scores ----
   float mx = -1e30f;
+#pragma unroll 2
   for (int i = lane; i < n_keys; i += 32) {
     const uint4* kr = reinterpret_cast<const uint4*>(kcache + cbase + static_cast<long long>(spos[w][i]) * 64);
     float s = 0.f;
+    uint4 kv[8];
+#pragma unroll
+    for (int c8 = 0; c8 < 8; ++c8) kv[c8] = kr[c8];   // the whole 128-byte row in flight at once
 #pragma unroll
     for (int c8 = 0; c8 < 8; ++c8) {
-      const uint4 u = kr[c8];
+      const uint4 u = kv[c8];
       float2 f;
       const float* qq = &sq[w][c8 * 8];
       f = unpack_bf16x2(u.x); s += f.x * qq[0] + f.y * qq[1];
@@ -190,13 +194,14 @@ decode_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restr
   // ---- phase 3: weighted sum of V rows; lane owns dims (2*lane, 2*lane+1) ----
   float a0 = 0.f, a1 = 0.f;
   int i = 0;
-  for (; i + 4 <= n_keys; i += 4) {
-    uint32_t vu[4];
+  // 16 V rows in flight per iteration: the loop is a chain of L2 round trips, not bandwidth
+  for (; i + 16 <= n_keys; i += 16) {
+    uint32_t vu[16];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 16; ++j)
       vu[j] = *reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[w][i + j]) * 64 + lane * 2);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 16; ++j) {
       const float2 vf = unpack_bf16x2(vu[j]);
       const float p = sp[w][i + j];
       a0 += p * vf.x;
