@@ -37,6 +37,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="micro-batch per GPU")
     ap.add_argument("--preset", default="ttt")
     ap.add_argument("--averaging", default="auto", choices=["auto", "fused", "nccl"])
+    ap.add_argument("--payload", default="fp32", choices=["fp32", "bf16", "u8"],
+                    help="gradient payload of the fused intra-box averaging kernel (u8 = uniform 8-bit, config 3)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -147,7 +149,7 @@ def main():
 
         trainer = EagerTrainer(cfg, dev)
     else:
-        trainer = GroupTrainer(cfg, dev, averaging=args.averaging, seed=0)
+        trainer = GroupTrainer(cfg, dev, averaging=args.averaging, seed=0, payload=args.payload)
 
     gen = torch.Generator().manual_seed(1234 + rank)
     n_batches = 4
@@ -227,6 +229,7 @@ def main():
                        "global_batch": B * world, "micro_batch_per_gpu": B, "seq_len": cfg.seq_len,
                        "parallelism": f"dp{world}", "optimizer": "LAMB-8bit, one update per step",
                        "averaging": getattr(trainer, "averaging", "n/a"),
+                       "averaging_payload": getattr(trainer, "payload", "n/a"),
                        "activations": activation_policy(trainer, B, cfg),
                        "l2": "per-step working set (>5 GB activations/weights) exceeds the 126 MB L2; no flush"},
             "exposed_averaging_ms_per_step": exposed_ms,

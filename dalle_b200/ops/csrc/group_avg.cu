@@ -45,7 +45,8 @@ struct GroupArgs {
   int n_blocks;                       // total blocks of the flat buffer
   int blk0, blk1;                     // my shard
   uint32_t epoch;                     // barrier values epoch+1 .. epoch+4 are used by this launch
-  int payload_mode;                   // 0 = fp32 P2P loads, 1 = bf16 payload
+  int payload_mode;                   // 0 = fp32 P2P loads, 1 = bf16 payload, 2 = uniform 8-bit payload
+                                      //     (int8 codes + one fp32 scale per 4096-element block)
   int zero_grad;
   int reduce_only;                    // 1: stop after the reduce phase and give EVERY rank the reduced gradient
   // local optimizer state (shard only is touched)
@@ -105,6 +106,40 @@ group_lamb_kernel(const GroupArgs a) {
       dst[i] = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
     }
   }
+  if (a.payload_mode == 2) {
+    // my gradients -> uniform 8-bit payload: per 4096-element block, code = rint(x * 127 / absmax) and one fp32
+    // step; a quarter of the fp32 NVLink bytes (the intra-box counterpart of hivemind's Uniform8BitQuantization)
+    int8_t* codes = reinterpret_cast<int8_t*>(a.payload[a.rank]);
+    float* steps = reinterpret_cast<float*>(codes + static_cast<long long>(a.n_blocks) * QBLOCK);
+    for (int b = blockIdx.x; b < a.n_blocks; b += gridDim.x) {
+      const float* src = a.grad[a.rank] + static_cast<long long>(b) * QBLOCK + e0;
+      float v[EPT];
+      float am = 0.f;
+#pragma unroll
+      for (int j = 0; j < EPT; j += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(src + j);
+        v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
+        am = fmaxf(am, fmaxf(fmaxf(fabsf(t.x), fabsf(t.y)), fmaxf(fabsf(t.z), fabsf(t.w))));
+        if (!(isfinite(t.x) && isfinite(t.y) && isfinite(t.z) && isfinite(t.w))) am = INFINITY;   // (fmaxf drops NaN)
+      }
+      am = block_max(am, sred);
+      // (a non-finite block keeps its NaN/Inf visible: the step becomes NaN and every code saturates)
+      const float step = am > 0.f ? am * (1.0f / 127.0f) : 1.0f;
+      const float inv = 1.0f / step;
+      uint32_t packed[EPT / 4];
+#pragma unroll
+      for (int j = 0; j < EPT; j += 4) {
+        const int q0 = __float2int_rn(v[j] * inv), q1 = __float2int_rn(v[j + 1] * inv);
+        const int q2 = __float2int_rn(v[j + 2] * inv), q3 = __float2int_rn(v[j + 3] * inv);
+        packed[j / 4] = (static_cast<uint32_t>(q0) & 0xffu) | ((static_cast<uint32_t>(q1) & 0xffu) << 8) |
+                        ((static_cast<uint32_t>(q2) & 0xffu) << 16) | ((static_cast<uint32_t>(q3) & 0xffu) << 24);
+      }
+      uint32_t* dst = reinterpret_cast<uint32_t*>(codes + static_cast<long long>(b) * QBLOCK + e0);
+#pragma unroll
+      for (int j = 0; j < EPT / 4; ++j) dst[j] = packed[j];
+      if (threadIdx.x == 0) steps[b] = isfinite(am) ? step : am;
+    }
+  }
   rank_barrier(a, a.epoch + 1, grid);  // phase 0: all gradients (and payloads) are complete
 
   // ---- phase 1: reduce-scatter into my shard -----------------------------------------------------
@@ -128,6 +163,18 @@ group_lamb_kernel(const GroupArgs a) {
           f = unpack_bf16x2(u.y); acc[j + 2] += f.x; acc[j + 3] += f.y;
           f = unpack_bf16x2(u.z); acc[j + 4] += f.x; acc[j + 5] += f.y;
           f = unpack_bf16x2(u.w); acc[j + 6] += f.x; acc[j + 7] += f.y;
+        }
+      } else if (a.payload_mode == 2) {
+        const int8_t* codes = reinterpret_cast<const int8_t*>(a.payload[src]);
+        const float step = reinterpret_cast<const float*>(codes + static_cast<long long>(a.n_blocks) * QBLOCK)[b];
+        const uint32_t* p = reinterpret_cast<const uint32_t*>(codes + base);
+#pragma unroll
+        for (int j = 0; j < EPT; j += 4) {
+          const uint32_t u = p[j / 4];
+          acc[j] += step * static_cast<float>(static_cast<int8_t>(u & 0xffu));
+          acc[j + 1] += step * static_cast<float>(static_cast<int8_t>((u >> 8) & 0xffu));
+          acc[j + 2] += step * static_cast<float>(static_cast<int8_t>((u >> 16) & 0xffu));
+          acc[j + 3] += step * static_cast<float>(static_cast<int8_t>(u >> 24));
         }
       } else {
         const float4* p = reinterpret_cast<const float4*>(a.grad[src] + base);

@@ -42,8 +42,9 @@ class FusedGroupAverager:
         self.grad, hg = alloc(n, torch.float32)
         self.param, hp = alloc(n, torch.float32)
         self.shadow, hs = alloc(n, torch.bfloat16)
-        self.payload_mode = {"fp32": 0, "bf16": 1}[payload]
-        self.payload, hpl = alloc(n if self.payload_mode == 1 else 8, torch.bfloat16)
+        self.payload_mode = {"fp32": 0, "bf16": 1, "u8": 2}[payload]
+        # bf16: 2 B / element; u8: 1 B / element + one fp32 step per 4096-element block (fits the same 2 B / element)
+        self.payload, hpl = alloc(n if self.payload_mode else 8, torch.bfloat16)
         self.xstride = (2 + 2 * f.n_tensors + 31) // 32 * 32
         self.xchg, hx = alloc(self.world * self.xstride, torch.float32)
         self.sig, hsig = alloc(64, torch.int32)

@@ -38,7 +38,7 @@ def param_groups(model: DALLE, weight_decay: float):
 class GroupTrainer:
     def __init__(self, cfg: DalleConfig, device, *, lr=2.5e-3, betas=(0.9, 0.96), eps=1e-6, weight_decay=0.045,
                  max_grad_norm=4.0, clamp_value=10000.0, warmup_steps=3125, total_steps=31250, seed=0,
-                 averaging: str = "auto", process_group=None):
+                 averaging: str = "auto", process_group=None, payload: Optional[str] = None):
         self.cfg, self.device = cfg, torch.device(device)
         self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if dist.is_initialized() else 0
@@ -58,7 +58,10 @@ class GroupTrainer:
         if self.world > 1 and averaging == "fused":
             from .parallel.group import FusedGroupAverager
 
-            self.group = FusedGroupAverager(self.opt, process_group)
+            # what a rank exposes to its peers over NVLink: fp32 gradients, a bf16 copy, or uniform 8-bit codes
+            payload = payload or os.environ.get("DALLE_B200_GROUP_PAYLOAD", "fp32")
+            self.payload = payload
+            self.group = FusedGroupAverager(self.opt, process_group, payload=payload)
         self.steps = 0
         from .utils.phases import PhaseTrace
 

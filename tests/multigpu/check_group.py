@@ -42,7 +42,7 @@ def main():
         torch.cuda.synchronize()
         assert not group.step_was_skipped()
         La, Lb = opt_a._fused.layout, opt_b._fused.layout
-        tol = 1e-3 if payload == "fp32" else 3e-3
+        tol = {"fp32": 1e-3, "bf16": 3e-3, "u8": 2e-2}[payload]
         err = (La.flat - Lb.flat).abs().max().item()
         assert err < tol, f"step {step}: fused vs nccl path differ by {err}"
         assert La.flat_grad.abs().max().item() == 0.0
@@ -53,7 +53,7 @@ def main():
         dist.broadcast(ref, src=0)
         assert torch.equal(mine, ref), "ranks diverged"
         gn_a, gn_b = group.grad_norm(), opt_b.grad_norm() / world  # the single-GPU entry reports the unscaled norm
-        assert abs(gn_a - gn_b) / gn_b < (1e-4 if payload == "fp32" else 1e-2), (gn_a, gn_b)
+        assert abs(gn_a - gn_b) / gn_b < {"fp32": 1e-4, "bf16": 1e-2, "u8": 2e-2}[payload], (gn_a, gn_b)
     # non-finite gradient on ONE rank: every rank skips the step
     before = opt_a._fused.layout.flat.clone()
     for p in ps_a:

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-@pytest.mark.parametrize("payload", ["fp32", "bf16"])
+@pytest.mark.parametrize("payload", ["fp32", "bf16", "u8"])
 def test_fused_group_step_matches_nccl_path(payload):
     n = torch.cuda.device_count()
     if n < 2:
