@@ -11,7 +11,7 @@
 //   warp 1  : TMEM allocator + MMA issuer (one lane)
 //   warps 2-9: epilogue, warp w owns TMEM lanes 32*(w%4)..+31 (one output row per thread) and one half of the
 //              256 accumulator columns
-#include "sm100_ptx.cuh"
+#include "sm100_cg2.cuh"
 #include "b200_api.h"
 #include <cstdlib>
 
@@ -31,8 +31,11 @@ constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int OUT_TILE_BYTES = 32 * 64;                 // 32 rows x 32 bf16, 64B-swizzled TMA-store box
 constexpr int OUT_TILES_PER_WARP = 3;
 constexpr int OUT_STAGE_BYTES = 8 * OUT_TILES_PER_WARP * OUT_TILE_BYTES;  // 48 KiB for the 8 epilogue warps
-__host__ __device__ constexpr int gemm_stages(int epi) {
-  return (epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4;   // (RESID_DEEP: 4)
+// cg = 2 (CTA pairs): each CTA stages its own A tile and HALF of the B tile, 32 KB per stage instead of 48 KB, so
+// the same shared memory holds a deeper ring
+__host__ __device__ constexpr int gemm_stage_bytes(int cg) { return A_STAGE_BYTES + B_STAGE_BYTES / cg; }
+__host__ __device__ constexpr int gemm_stages(int epi, int cg = 1) {
+  return ((epi == B200_EPI_GEGLU_BWD || epi == B200_EPI_RESID) ? 3 : 4) * (cg == 2 ? 3 : 2) / 2;   // 3|4 -> 4|6
 }
 // Epilogue warps per CTA: 4 per TMEM lane quarter x column parts.  (16 warps were measured on the GEGLU backward
 // epilogue: no gain.  An ablation showed why: that kernel's time is its 1.3 GB of epilogue loads + stores, whose
@@ -49,8 +52,9 @@ __host__ __device__ constexpr int gemm_out_tiles(int epi) {   // staging tiles p
 __host__ __device__ constexpr int gemm_out_stage_bytes(int epi) {
   return gemm_epi_warps(epi) * gemm_out_tiles(epi) * OUT_TILE_BYTES;
 }
-__host__ __device__ constexpr int gemm_smem_bytes(int epi) {
-  return gemm_stages(epi) * STAGE_BYTES + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ + 1024 /*barriers, column-sum scratch*/;
+__host__ __device__ constexpr int gemm_smem_bytes(int epi, int cg = 1) {
+  return gemm_stages(epi, cg) * gemm_stage_bytes(cg) + gemm_out_stage_bytes(epi) + 1024 /*align slack*/ +
+         1024 /*barriers, column-sum scratch*/;
 }
 constexpr int TMEM_COLS = 512;  // 2 accumulator stages x 256 fp32 columns
 
@@ -74,19 +78,27 @@ struct GemmDev {
   int n_half;
   float alpha;
   float* a_colsum;     // TN only: a_colsum[m] += sum_k A[k, m], taken from the A tiles in shared memory
+  int cg;              // 1, or 2: CTA pairs (cta_group::2) - a unit is then a PAIR of vertically adjacent tiles
 };
 
-// The i-th work unit of this CTA: output tile t, k-blocks [kb0, kb1).
-struct GemmUnit { int t, kb0, kb1; };
+// The i-th work unit of this CTA: output tile (m_blk, n_blk), k-blocks [kb0, kb1).  With CTA pairs the grid is walked
+// pair by pair: both CTAs of a pair get the same unit index, the same n_blk and m_blk = 2 * pair_row + rank.
+struct GemmUnit { int t, m_blk, n_blk, kb0, kb1; };
 __device__ __forceinline__ bool gemm_unit(const GemmDev& g, int i, GemmUnit& un) {
-  const int u = blockIdx.x + i * gridDim.x;
-  if (u >= g.m_tiles * g.n_tiles * g.splits) return false;
+  const int cta = g.cg == 2 ? (blockIdx.x >> 1) : blockIdx.x;
+  const int ncta = g.cg == 2 ? (gridDim.x >> 1) : gridDim.x;
+  const int m_rows = g.cg == 2 ? (g.m_tiles + 1) / 2 : g.m_tiles;   // tile rows (pairs of tile rows)
+  const int u = cta + i * ncta;
+  const int tiles = m_rows * g.n_tiles;
+  if (u >= tiles * g.splits) return false;
   const int kb_per = (g.kb_total + g.splits - 1) / g.splits;
   // split-major order: the units of one wave share a K range, so every A / B panel of that range is pulled from
   // HBM once and then served by L2 (tile-major order re-read the large operand once per split wave)
-  const int tiles = g.m_tiles * g.n_tiles;
   const int split = u / tiles;
   un.t = u - split * tiles;
+  un.n_blk = un.t % g.n_tiles;
+  un.m_blk = un.t / g.n_tiles;
+  if (g.cg == 2) un.m_blk = un.m_blk * 2 + (blockIdx.x & 1);
   un.kb0 = split * kb_per;
   un.kb1 = min(un.kb0 + kb_per, g.kb_total);
   return true;
@@ -179,12 +191,14 @@ __device__ __forceinline__ void store_row_bf16(__nv_bfloat16* rowp, int col, int
   }
 }
 
-template <int A_MN, int B_MN, int EPI>
+template <int A_MN, int B_MN, int EPI, int CG>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmO2,
             const __grid_constant__ CUtensorMap tmX, const GemmDev g) {
-  constexpr int STAGES = gemm_stages(EPI);
+  constexpr int STAGES = gemm_stages(EPI, CG);
+  constexpr int B_BYTES = B_STAGE_BYTES / CG;              // B rows staged per CTA: 256, or 128 of a pair's 256
+  constexpr int STAGE_BYTES = gemm_stage_bytes(CG);
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = smem_u32(smem_raw);
   const uint32_t pad = ((raw_addr + 1023u) & ~1023u) - raw_addr;
@@ -199,6 +213,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
   uint64_t* aux_bar = bars + 2 * STAGES + 6;     // [epilogue warps][2 sets]: TMA loads of epilogue inputs (aux / residual)
+  // CTA pairs: rank 0 (the leader) issues the MMAs of both; the pair's full / accumulator-empty barriers are the
+  // leader's, the stage-empty and accumulator-full barriers are signalled in both CTAs by multicast commits
+  const uint32_t crank = CG == 2 ? cluster_ctarank() : 0u;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -212,18 +229,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 32 * gemm_epi_warps(EPI));
+      mbar_init(&tempty_bar[s], 32 * gemm_epi_warps(EPI) * CG);   // (pairs: both CTAs' epilogue threads)
     }
     if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP || EPI == B200_EPI_ATOMIC_F32)
       for (int s = 0; s < 2 * gemm_epi_warps(EPI); ++s) mbar_init(&aux_bar[s], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    if (CG == 2) { tmem_alloc_cg2(tmem_slot, TMEM_COLS); tmem_relinquish_cg2(); }
+    else { tmem_alloc(tmem_slot, TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();   // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -234,34 +252,53 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t phase = 0;
       GemmUnit un;
       for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
-        const int n_blk = un.t % g.n_tiles, m_blk = un.t / g.n_tiles;
+        const int n_blk = un.n_blk, m_blk = un.m_blk;
         const int m0 = m_blk * BM, n0 = n_blk * g.tile_n_step;
         for (int kb = un.kb0; kb < un.kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
-          uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
+          uint8_t* sb = smem_b + stage * B_BYTES;
           const int k0 = kb * BK;
-          if (A_MN == 0) {
-            tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);  // box {64 k, 128 m}
-          } else {
-            tma_load_2d(sa, &tmA, &full_bar[stage], m0, k0);  // box {64 m, 64 k}
-            tma_load_2d(sa + 8192, &tmA, &full_bar[stage], m0 + 64, k0);
-          }
-          if (B_MN == 0) {
-            tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);  // box {64 k, 128 n}
-            tma_load_2d(sb + 16384, &tmB, &full_bar[stage], k0, n0 + g.second_off);
-          } else {
+          if (CG == 2) {
+            // my A tile and my half of the pair's B tile; the bytes of both CTAs complete the LEADER's barrier
+            if (crank == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+            const uint32_t fb = map_to_cta(&full_bar[stage], 0);
+            if (A_MN == 0) {
+              tma_load_2d_cg2(sa, &tmA, fb, k0, m0);
+            } else {
+              tma_load_2d_cg2(sa, &tmA, fb, m0, k0);
+              tma_load_2d_cg2(sa + 8192, &tmA, fb, m0 + 64, k0);
+            }
+            if (B_MN == 0) {
+              tma_load_2d_cg2(sb, &tmB, fb, k0, n0 + static_cast<int>(crank) * g.second_off);
+            } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) tma_load_2d(sb + i * 8192, &tmB, &full_bar[stage], n0 + 64 * i, k0);
+              for (int i = 0; i < 2; ++i)
+                tma_load_2d_cg2(sb + i * 8192, &tmB, fb, n0 + 128 * static_cast<int>(crank) + 64 * i, k0);
+            }
+          } else {
+            mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+            if (A_MN == 0) {
+              tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);  // box {64 k, 128 m}
+            } else {
+              tma_load_2d(sa, &tmA, &full_bar[stage], m0, k0);  // box {64 m, 64 k}
+              tma_load_2d(sa + 8192, &tmA, &full_bar[stage], m0 + 64, k0);
+            }
+            if (B_MN == 0) {
+              tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);  // box {64 k, 128 n}
+              tma_load_2d(sb + 16384, &tmB, &full_bar[stage], k0, n0 + g.second_off);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) tma_load_2d(sb + i * 8192, &tmB, &full_bar[stage], n0 + 64 * i, k0);
+            }
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && crank == 0) {   // (pairs: the leader issues for both CTAs)
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -276,22 +313,26 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
-          const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+          const uint32_t sb = smem_u32(smem_b + stage * B_BYTES);
 #pragma unroll
           for (int kk = 0; kk < BK / 16; ++kk) {
             // K-major: 8-row groups 1024 B apart, +32 B per 16-element k step inside the swizzle row.
             // MN-major: 64-element MN atoms 8192 B apart (LBO), 8-k-row groups 1024 B apart (SBO),
             //           +2048 B per 16 k rows.
+            // (pairs: the descriptors name the leader's tiles; the peer's sit at the same offsets)
             const uint64_t ad = A_MN ? make_smem_desc_sw128(sa + kk * 2048, 8192, 1024)
                                      : make_smem_desc_sw128(sa + kk * 32, 0, 1024);
             const uint64_t bd = B_MN ? make_smem_desc_sw128(sb + kk * 2048, 8192, 1024)
                                      : make_smem_desc_sw128(sb + kk * 32, 0, 1024);
-            umma_bf16_ss(tmem_d, ad, bd, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+            if (CG == 2) umma_bf16_ss_cg2(tmem_d, ad, bd, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
+            else umma_bf16_ss(tmem_d, ad, bd, idesc, (kb > kb0 || kk > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);
+          if (CG == 2) umma_commit_cg2(&empty_bar[stage], 0x3);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[acc]);
+        if (CG == 2) umma_commit_cg2(&tfull_bar[acc], 0x3);
+        else umma_commit(&tfull_bar[acc]);
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1;
       }
@@ -314,7 +355,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       uint32_t n_ld = 0, n_use = 0;   // boxes requested / consumed: buffer = n & 1, parity = (n >> 1) & 1
       GemmUnit un;
       for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
-        const int n_blk = un.t % g.n_tiles, m_blk = un.t / g.n_tiles;
+        const int n_blk = un.n_blk, m_blk = un.m_blk;
         const int mcol = m_blk * BM + box * 64;
         // first k-block of this unit that falls to it: kb = n_blk (mod n_tiles)
         int kb_first = un.kb0 + ((n_blk - un.kb0 % g.n_tiles) + g.n_tiles) % g.n_tiles;
@@ -428,20 +469,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_expect_tx(&my_aux_bar[set], 2 * OUT_TILE_BYTES);
       tma_load_2d(stage + (2 * set) * OUT_TILE_BYTES, &tmX, &my_aux_bar[set], x, y);
     };
-    if ((EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) && blockIdx.x < g.m_tiles * g.n_tiles && lane == 0) {
-      const int t0 = blockIdx.x;   // (these epilogues never split K)
-      const int x0 = (t0 % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
-      if (x0 < g.N) {
-        if (EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) res_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
-        else aux_load(0, x0, (t0 / g.n_tiles) * BM + q * 32);
+    if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) {
+      GemmUnit u0;   // the first chunk of the CTA's first unit is requested before the loop
+      if (gemm_unit(g, 0, u0) && lane == 0) {
+        const int x0 = u0.n_blk * g.tile_n_step + cpart * NCH * 32;
+        if (x0 < g.N) {
+          if (EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) res_load(0, x0, u0.m_blk * BM + q * 32);
+          else aux_load(0, x0, u0.m_blk * BM + q * 32);
+        }
       }
     }
     int acc = 0;
     uint32_t acc_phase = 0;
     GemmUnit un;
     for (int ui = 0; gemm_unit(g, ui, un); ++ui) {
-      const int t = un.t;
-      const int n_blk = t % g.n_tiles, m_blk = t / g.n_tiles;
+      const int n_blk = un.n_blk, m_blk = un.m_blk;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * g.tile_n_step;
       const bool row_ok = row < g.M;
@@ -499,8 +541,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           if (!have) {
             GemmUnit nx;
             have = gemm_unit(g, ui + 1, nx);
-            ncol = (nx.t % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
-            ny = (nx.t / g.n_tiles) * BM + q * 32;
+            ncol = nx.n_blk * g.tile_n_step + cpart * NCH * 32;
+            ny = nx.m_blk * BM + q * 32;
           }
           if (have && ncol < g.N) {
             stage_reuse();   // the stores that last read that set are done with it
@@ -597,8 +639,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (!have) {
               GemmUnit nx;
               have = gemm_unit(g, ui + 1, nx);
-              ncol = (nx.t % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
-              ny = (nx.t / g.n_tiles) * BM + q * 32;
+              ncol = nx.n_blk * g.tile_n_step + cpart * NCH * 32;
+              ny = nx.m_blk * BM + q * 32;
             }
             if (have && ncol < g.N) {
               stage_reuse();
@@ -623,8 +665,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (!have) {
               GemmUnit nx;
               have = gemm_unit(g, ui + 1, nx);
-              ncol = (nx.t % g.n_tiles) * g.tile_n_step + cpart * NCH * 32;
-              ny = (nx.t / g.n_tiles) * BM + q * 32;
+              ncol = nx.n_blk * g.tile_n_step + cpart * NCH * 32;
+              ny = nx.m_blk * BM + q * 32;
             }
             if (have && ncol < g.N) {
               stage_reuse();
@@ -745,7 +787,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         }
       }
       tc_fence_before();
-      mbar_arrive(&tempty_bar[acc]);
+      if (CG == 2 && crank != 0) mbar_arrive_remote(map_to_cta(&tempty_bar[acc], 0));   // the leader's barrier
+      else mbar_arrive(&tempty_bar[acc]);
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
@@ -754,9 +797,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();   // nobody leaves (or frees TMEM) while the peer can still signal or read
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) tmem_dealloc_cg2(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -851,18 +896,40 @@ int num_sms() {
 
 static CUtensorMap g_tm_out, g_tm_out2, g_tm_x;  // set by b200_gemm_bf16 before launch<>() (host-side, per call)
 
-template <int A_MN, int B_MN, int EPI>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
-  auto kern = gemm_kernel<A_MN, B_MN, EPI>;
-  constexpr int smem = gemm_smem_bytes(EPI);
+template <int A_MN, int B_MN, int EPI, int CG>
+static int launch_cg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
+  auto kern = gemm_kernel<A_MN, B_MN, EPI, CG>;
+  constexpr int smem = gemm_smem_bytes(EPI, CG);
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return -3;
     configured = true;
   }
-  kern<<<grid, gemm_threads(EPI), smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g_tm_x, g);
+  if (CG == 1) {
+    kern<<<grid, gemm_threads(EPI), smem, st>>>(ta, tb, g_tm_out, g_tm_out2, g_tm_x, g);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(gemm_threads(EPI));
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (cudaLaunchKernelEx(&cfg, kern, ta, tb, g_tm_out, g_tm_out2, g_tm_x, g) != cudaSuccess) return -4;
+  }
   return cudaGetLastError() == cudaSuccess ? 0 : -4;
+}
+
+template <int A_MN, int B_MN, int EPI>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
+  if (g.cg == 2) return launch_cg<A_MN, B_MN, EPI, 2>(ta, tb, g, grid, st);
+  return launch_cg<A_MN, B_MN, EPI, 1>(ta, tb, g, grid, st);
 }
 
 }  // namespace b200
@@ -908,7 +975,30 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
     g.n_tiles = (d->N + BN - 1) / BN;
   }
   int splits = d->splits;
-  const int tiles = g.m_tiles * g.n_tiles;
+  // CTA pairs (cta_group::2).  Measured on the TTT shapes: pairs win where the mainloop is the bound (long K, many
+  // tiles: FF2 329 -> 268 us, wgrad FF2 374 -> 294 us, dgrad / wgrad QKV -10 %, GEGLU forward -4 %) and lose where the
+  // epilogue is (the leader's MMA then waits for the slower of TWO epilogues: GEGLU backward, K = 1024 residual).
+  // B200_GEMM_CG2 = bit mask of (1 << epi) overrides the policy (experiments).
+  int cg = 1;
+  if (d->M > BM && num_sms() % 2 == 0) {
+    static int mask = -2;
+    if (mask == -2) { const char* e = getenv("B200_GEMM_CG2"); mask = e ? atoi(e) : -1; }
+    bool pair;
+    if (mask >= 0) {
+      pair = (mask >> d->epi) & 1;
+    } else {
+      const int n_tiles_all = g.m_tiles * g.n_tiles;
+      switch (d->epi) {
+        case B200_EPI_GEGLU: pair = true; break;
+        case B200_EPI_RESID: pair = d->K >= 2048; break;
+        case B200_EPI_BF16: pair = d->K >= 2048; break;
+        case B200_EPI_ATOMIC_F32: pair = n_tiles_all >= 64 && !resid_atomic; break;
+        default: pair = false;
+      }
+    }
+    if (pair) cg = 2;
+  }
+  const int tiles = (cg == 2 ? (g.m_tiles + 1) / 2 : g.m_tiles) * g.n_tiles;   // units per split (pairs count once)
   if (splits <= 0) {
     splits = 1;
     if (d->epi == B200_EPI_ATOMIC_F32) {
@@ -916,7 +1006,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
       // = units / (waves * #SMs); every extra split costs one more accumulating epilogue per tile
       // (an equal-share stream-K cut of the k-block space measured 1.5x SLOWER here: CTAs at unrelated K
       // offsets lose the L2 reuse of the A / B panels that lock-step units share)
-      const int sms = num_sms();
+      const int sms = num_sms() / cg;
       const int min_kb = resid_atomic ? 4 : 32;   // k-blocks per unit
       const int max_splits = g.kb_total / min_kb > 0 ? (g.kb_total / min_kb < 16 ? g.kb_total / min_kb : 16) : 1;
       float best = -1.f;
@@ -947,6 +1037,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
   g.aux = reinterpret_cast<const __nv_bfloat16*>(d->aux); g.ldaux = d->ldaux;
   g.n_half = d->n_half;
   g.alpha = d->alpha;
+  g.cg = cg;
   if (d->a_colsum && !(a_mn && d->epi == B200_EPI_ATOMIC_F32)) return -16;
   if (d->epi == B200_EPI_ATOMIC_F32 && !resid_atomic) g.scale = nullptr;
   g.a_colsum = d->a_colsum;
@@ -991,7 +1082,7 @@ extern "C" int b200_gemm_bf16(const B200Gemm* d_in, void* stream) {
     }
   }
   const int units = tiles * splits;
-  const int grid = units < num_sms() ? units : num_sms();
+  const int grid = cg * (units < num_sms() / cg ? units : num_sms() / cg);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
 
 #define B200_DISPATCH_EPI(AMN, BMN)                                                              \
