@@ -104,117 +104,138 @@ __global__ void decode_ln_shift_kernel(const float* __restrict__ x, const float*
   }
 }
 
-// one warp per (sample, head).  Phase 1: lanes <-> keys (each lane dots q with whole K rows, independent loads);
-// phase 2: warp softmax; phase 3: lanes <-> head dims, streaming the V rows (coalesced 128 B per key).
+// one block of 4 warps per (sample, head); the key list is dealt to the warps in groups of 32.  Phase 1: lanes <-> keys
+// (each lane dots q with whole K rows, 128 bytes in flight per key); phase 2: block softmax; phase 3: lanes <-> head
+// dims, 16 V rows in flight per warp; the four partial outputs meet in shared memory.  (One warp per (sample, head)
+// left 4 warps per SM chasing L2 round trips: 26 us per layer.)
 constexpr int DEC_MAX_KEYS = 352;   // 257 text + 32 axial (+ window) rounded up
 __global__ void __launch_bounds__(128)
 decode_attn_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ kcache,
                    __nv_bfloat16* __restrict__ vcache, __nv_bfloat16* __restrict__ out,
                    const int* __restrict__ pos_ptr, DecGeom g, int mode) {
-  __shared__ float sq[4][64];
-  __shared__ float sp[4][DEC_MAX_KEYS];
-  __shared__ int spos[4][DEC_MAX_KEYS];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int wid = blockIdx.x * 4 + w;
+  __shared__ float sq[64];
+  __shared__ float sp[DEC_MAX_KEYS];
+  __shared__ int spos[DEC_MAX_KEYS];
+  __shared__ float sred[2][4];
+  __shared__ float sacc[4][64];
+  __shared__ int s_cnt;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+  const int wid = blockIdx.x;
   if (wid >= g.B * g.H) return;
   const int b = wid / g.H, h = wid - b * g.H, pos = *pos_ptr;
   const int HD = g.H * 64;
-  const __nv_bfloat16* row = qkv + static_cast<long long>(b) * 3 * HD + h * 64 + lane * 2;
-  const float2 q = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(row));
+  const __nv_bfloat16* row = qkv + static_cast<long long>(b) * 3 * HD + h * 64;
   const long long cbase = (static_cast<long long>(b) * g.H + h) * g.seq * 64;
-  *reinterpret_cast<uint32_t*>(kcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) =
-      *reinterpret_cast<const uint32_t*>(row + HD);
-  *reinterpret_cast<uint32_t*>(vcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) =
-      *reinterpret_cast<const uint32_t*>(row + 2 * HD);
-  sq[w][lane * 2] = q.x;
-  sq[w][lane * 2 + 1] = q.y;
+  if (w == 0) {
+    const float2 q = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(row + lane * 2));
+    sq[lane * 2] = q.x;
+    sq[lane * 2 + 1] = q.y;
+  } else if (w == 1) {
+    *reinterpret_cast<uint32_t*>(kcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) =
+        *reinterpret_cast<const uint32_t*>(row + HD + lane * 2);
+  } else if (w == 2) {
+    *reinterpret_cast<uint32_t*>(vcache + cbase + static_cast<long long>(pos) * 64 + lane * 2) =
+        *reinterpret_cast<const uint32_t*>(row + 2 * HD + lane * 2);
+  }
 
   // ---- the list of key positions this query may attend to ----
   int n_keys;
   if (pos < g.T) {
     n_keys = pos + 1;
-    for (int i = lane; i < n_keys; i += 32) spos[w][i] = i;
+    for (int i = tid; i < n_keys; i += 128) spos[i] = i;
   } else {
-    for (int i = lane; i < g.T; i += 32) spos[w][i] = i;
+    for (int i = tid; i < g.T; i += 128) spos[i] = i;
     const int p = pos - g.T, r = p / g.F, c = p - r * g.F;
     if (mode == 1) {
       n_keys = g.T + c + 1;
-      for (int i = lane; i <= c; i += 32) spos[w][g.T + i] = g.T + r * g.F + i;
+      for (int i = tid; i <= c; i += 128) spos[g.T + i] = g.T + r * g.F + i;
     } else if (mode == 2) {
       n_keys = g.T + r + 1;
-      for (int i = lane; i <= r; i += 32) spos[w][g.T + i] = g.T + i * g.F + c;
+      for (int i = tid; i <= r; i += 128) spos[g.T + i] = g.T + i * g.F + c;
     } else if (mode == 3) {
-      int cnt = 0;
-      if (lane == 0) {
+      if (tid == 0) {
+        int cnt = 0;
         for (int rr = max(0, r - g.conv_half); rr <= r; ++rr)
           for (int cc = max(0, c - g.conv_half); cc <= min(g.F - 1, c + g.conv_half); ++cc)
-            if (rr * g.F + cc <= p) spos[w][g.T + cnt++] = g.T + rr * g.F + cc;
+            if (rr * g.F + cc <= p) spos[g.T + cnt++] = g.T + rr * g.F + cc;
+        s_cnt = cnt;
       }
-      n_keys = g.T + __shfl_sync(0xffffffffu, cnt, 0);
+      __syncthreads();
+      n_keys = g.T + s_cnt;
     } else {
       n_keys = min(pos + 1, DEC_MAX_KEYS);
-      for (int i = g.T + lane; i < n_keys; i += 32) spos[w][i] = i;
+      for (int i = g.T + tid; i < n_keys; i += 128) spos[i] = i;
     }
   }
-  __syncwarp();
+  __syncthreads();   // key list, q, and this position's K / V rows (global writes by this block) are in place
 
-  // ---- phase 1: scores ----
+  // ---- phase 1: scores (thread tid takes keys tid, tid + 128, ...) ----
   float mx = -1e30f;
-#pragma unroll 2
-  for (int i = lane; i < n_keys; i += 32) {
-    const uint4* kr = reinterpret_cast<const uint4*>(kcache + cbase + static_cast<long long>(spos[w][i]) * 64);
-    float s = 0.f;
+  for (int i = tid; i < n_keys; i += 128) {
+    const uint4* kr = reinterpret_cast<const uint4*>(kcache + cbase + static_cast<long long>(spos[i]) * 64);
     uint4 kv[8];
 #pragma unroll
     for (int c8 = 0; c8 < 8; ++c8) kv[c8] = kr[c8];   // the whole 128-byte row in flight at once
+    float sc = 0.f;
 #pragma unroll
     for (int c8 = 0; c8 < 8; ++c8) {
       const uint4 u = kv[c8];
       float2 f;
-      const float* qq = &sq[w][c8 * 8];
-      f = unpack_bf16x2(u.x); s += f.x * qq[0] + f.y * qq[1];
-      f = unpack_bf16x2(u.y); s += f.x * qq[2] + f.y * qq[3];
-      f = unpack_bf16x2(u.z); s += f.x * qq[4] + f.y * qq[5];
-      f = unpack_bf16x2(u.w); s += f.x * qq[6] + f.y * qq[7];
+      const float* qq = &sq[c8 * 8];
+      f = unpack_bf16x2(u.x); sc += f.x * qq[0] + f.y * qq[1];
+      f = unpack_bf16x2(u.y); sc += f.x * qq[2] + f.y * qq[3];
+      f = unpack_bf16x2(u.z); sc += f.x * qq[4] + f.y * qq[5];
+      f = unpack_bf16x2(u.w); sc += f.x * qq[6] + f.y * qq[7];
     }
-    s *= kLog2eDec;
-    sp[w][i] = s;
-    mx = fmaxf(mx, s);
+    sc *= kLog2eDec;
+    sp[i] = sc;
+    mx = fmaxf(mx, sc);
   }
   mx = warp_max(mx);
+  if (lane == 0) sred[0][w] = mx;
+  __syncthreads();
+  mx = fmaxf(fmaxf(sred[0][0], sred[0][1]), fmaxf(sred[0][2], sred[0][3]));
   // ---- phase 2: probabilities ----
   float l = 0.f;
-  for (int i = lane; i < n_keys; i += 32) {
-    const float p = exp2f(sp[w][i] - mx);
-    sp[w][i] = p;
+  for (int i = tid; i < n_keys; i += 128) {
+    const float p = exp2f(sp[i] - mx);
+    sp[i] = p;
     l += p;
   }
   l = warp_sum(l);
-  __syncwarp();
-  // ---- phase 3: weighted sum of V rows; lane owns dims (2*lane, 2*lane+1) ----
+  if (lane == 0) sred[1][w] = l;
+  __syncthreads();
+  l = (sred[1][0] + sred[1][1]) + (sred[1][2] + sred[1][3]);
+  // ---- phase 3: weighted sum of V rows; lane owns dims (2*lane, 2*lane+1); warp w takes keys w, w + 4, ... ----
   float a0 = 0.f, a1 = 0.f;
-  int i = 0;
-  // 16 V rows in flight per iteration: the loop is a chain of L2 round trips, not bandwidth
-  for (; i + 16 <= n_keys; i += 16) {
+  int i = w;
+  for (; i + 60 < n_keys; i += 64) {   // 16 rows of this warp in flight
     uint32_t vu[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j)
-      vu[j] = *reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[w][i + j]) * 64 + lane * 2);
+      vu[j] = *reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[i + 4 * j]) * 64 + lane * 2);
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
       const float2 vf = unpack_bf16x2(vu[j]);
-      const float p = sp[w][i + j];
+      const float p = sp[i + 4 * j];
       a0 += p * vf.x;
       a1 += p * vf.y;
     }
   }
-  for (; i < n_keys; ++i) {
-    const float2 vf = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[w][i]) * 64 + lane * 2));
-    a0 += sp[w][i] * vf.x;
-    a1 += sp[w][i] * vf.y;
+  for (; i < n_keys; i += 4) {
+    const float2 vf = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(vcache + cbase + static_cast<long long>(spos[i]) * 64 + lane * 2));
+    a0 += sp[i] * vf.x;
+    a1 += sp[i] * vf.y;
   }
-  const float inv = 1.0f / l;
-  *reinterpret_cast<uint32_t*>(out + static_cast<long long>(b) * HD + h * 64 + lane * 2) = pack_bf16x2(a0 * inv, a1 * inv);
+  sacc[w][lane * 2] = a0;
+  sacc[w][lane * 2 + 1] = a1;
+  __syncthreads();
+  if (w == 0) {
+    const float inv = 1.0f / l;
+    const float o0 = (sacc[0][lane * 2] + sacc[1][lane * 2]) + (sacc[2][lane * 2] + sacc[3][lane * 2]);
+    const float o1 = (sacc[0][lane * 2 + 1] + sacc[1][lane * 2 + 1]) + (sacc[2][lane * 2 + 1] + sacc[3][lane * 2 + 1]);
+    *reinterpret_cast<uint32_t*>(out + static_cast<long long>(b) * HD + h * 64 + lane * 2) = pack_bf16x2(o0 * inv, o1 * inv);
+  }
 }
 
 __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
@@ -387,7 +408,7 @@ extern "C" int b200_decode_attn(const void* qkv, void* kcache, void* vcache, voi
                                 int H, int seq, int T, int F, int mode, int conv_kernel, void* stream) {
   DecGeom g{B, H * 64, H, seq, T, F, conv_kernel / 2};
   if (T + F + 32 > DEC_MAX_KEYS && mode != 0) return -74;
-  decode_attn_kernel<<<(B * H + 3) / 4, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+  decode_attn_kernel<<<B * H, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(kcache),
       reinterpret_cast<__nv_bfloat16*>(vcache), reinterpret_cast<__nv_bfloat16*>(out), pos_ptr, g, mode);
   return derr();
