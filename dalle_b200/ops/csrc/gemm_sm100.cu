@@ -894,7 +894,8 @@ int num_sms() {
   return n;
 }
 
-static CUtensorMap g_tm_out, g_tm_out2, g_tm_x;  // set by b200_gemm_bf16 before launch<>() (host-side, per call)
+// set by b200_gemm_bf16 before launch<>() (host-side, per call; thread_local: host threads may call concurrently)
+static thread_local CUtensorMap g_tm_out, g_tm_out2, g_tm_x;
 
 template <int A_MN, int B_MN, int EPI, int CG>
 static int launch_cg(const CUtensorMap& ta, const CUtensorMap& tb, const GemmDev& g, int grid, cudaStream_t st) {
