@@ -35,7 +35,6 @@ struct AttnBwdArgs {
   const float2* rot_t;  // [32][seq+1] pair-major copy (coalesced for thread-per-row access)
   int rot_len;
   float q_scale;
-  int debug_skip_atomics;
 };
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -366,7 +365,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
             // touches 32 different rows = 32 L1 wavefronts; the warp's own slice of the P / dS buffers (dead
             // until the next chunk) transposes the 32 x 32 tile so that an instruction covers four whole
             // 128-byte row segments instead.
-            if (a.debug_skip_atomics) continue;
             uint8_t* stg = (half == 0 ? sP : sDS) + part * 16384 + qw * 4096;
 #pragma unroll
             for (int c8 = 0; c8 < 8; ++c8)
@@ -491,7 +489,6 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   a.g = g; a.lse = lse; a.out = reinterpret_cast<const __nv_bfloat16*>(out); (void)delta; a.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv); a.kv_acc = kv_acc;
   a.rot = reinterpret_cast<const float2*>(rot); a.q_scale = q_scale;
   a.rot_t = reinterpret_cast<const float2*>(rot_t); a.rot_len = seq + 1;
-  a.debug_skip_atomics = getenv("B200_ATTN_SKIP_KV_ATOMICS") != nullptr;
 
   CUtensorMap tq, ttail, tqcol, tdo, tdocol;
   int rc = attn_make_maps(qkv, g, ATT_COL, &tq, &ttail, &tqcol);
