@@ -117,7 +117,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
   constexpr uint32_t TM_S = 0, TM_DP = 128, TM_DQ = 256, TM_DK = 320, TM_DV = 384;
 
   if (warp == 0) {
-    if (lane == 0) {
+    // elect.sync (not `lane == 0`): single-thread region known to the compiler -> TMA / MMA operands stay in uniform
+    // registers instead of a make-uniform loop around every instruction
+    if (elect_one()) {
       const int row_base = b * g.seq;
       const int lines = 128 / g.F;
       // Q and dO
@@ -159,7 +161,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_wait(bar_q, 0);
       const uint32_t q_addr = smem_u32(sQ), do_addr = smem_u32(sDO), p_addr = smem_u32(sP), ds_addr = smem_u32(sDS);
       constexpr uint32_t id_dq = make_idesc_bf16(128, 64, 0, 1);

@@ -19,6 +19,7 @@ namespace b200 {
 
 int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
                    CUtensorMap* taux);
+int attn3_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode, cudaStream_t st);
 
 constexpr int AF2_THREADS = 128;
 constexpr int AF2_MAXK = 144;                       // keys per chunk
@@ -138,7 +139,9 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constan
       }
     }
   };
-  if (threadIdx.x == 0) {
+  // single-thread TMA / MMA issue goes through elect.sync on warp 0 (the compiler then keeps the operands in uniform
+  // registers; `threadIdx.x == 0` put a make-uniform loop around every instruction)
+  if (warp == 0 && elect_one()) {
     mbar_expect_tx(bar_q, 16384);
     if (MODE == ATT_COL) {
       for (int l = 0; l < lines; ++l) tma_load_4d(sQ + l * g.F * 128, &tmAux, bar_q, h * 64, blk * lines + l, 0, b);
@@ -172,7 +175,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tm128, const __grid_constan
                    make_smem_desc_sw128(v_addr + k16 * 2048, 8192, 1024), idesc_pv, k16 > 0 ? 1u : 0u);
     umma_commit(bar_o);
   };
-  if (threadIdx.x == 0) issue_s(0);
+  if (warp == 0 && elect_one()) issue_s(0);
   __syncwarp();
 
 #include "attn_fwd2_softmax.inc"
@@ -214,6 +217,14 @@ extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int 
   // wider grids take the first-generation kernel, which keeps whole score rows in TMEM
   if (32 % F) return b200_attn_fwd_v1(qkv, out, lse, B, H, seq, T, F, mode, conv_kernel, stream);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // DALLE_B200_ATTN_V3=1 routes text + axial patterns to the persistent pipelined kernel (attn3_fwd_sm100.cu): correct
+  // (same tests), but at the benchmark shapes still slower than this one (370 vs 265 us at batch 32) - its timeline
+  // and the MMA-latency probe are in profiles/attn3_fwd_timeline_r2.txt
+  static const bool v3 = getenv("DALLE_B200_ATTN_V3") != nullptr;
+  if (v3) {
+    const int rc3 = attn3_fwd(qkv, out, lse, B, H, seq, T, F, mode, st);
+    if (rc3 <= 0) return rc3;
+  }
   AttnFwd2Args a;
   a.g = g; a.out = reinterpret_cast<__nv_bfloat16*>(out); a.lse = lse; a.ld_out = H * 64;
   CUtensorMap t128, ttail, taux;

@@ -247,7 +247,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 
 
   if (warp == 0) {
-    if (lane == 0) {
+    // elect.sync, not `lane == 0`: the compiler then knows the region runs on one thread and keeps TMA / MMA operands
+    // in uniform registers; with `lane == 0` every cp.async.bulk.tensor and tcgen05.mma sat in its own
+    // make-uniform loop (309 of them in this file's SASS)
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       GemmUnit un;
@@ -297,7 +300,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && crank == 0) {   // (pairs: the leader issues for both CTAs)
+    if (crank == 0 && elect_one()) {   // (pairs: the leader issues for both CTAs)
       constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
@@ -363,7 +366,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[0][e] = acc[1][e] = 0.f;
         auto request = [&](int kb) {
-          if (lane == 0) {
+          if (elect_one()) {
             mbar_expect_tx(&lbar[n_ld & 1], 8192);
             tma_load_2d(buf + (n_ld & 1) * 8192, &tmA, &lbar[n_ld & 1], mcol, kb * BK);
           }
@@ -435,21 +438,23 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         *reinterpret_cast<uint4*>(base + ((p ^ sw) << 4)) = u;
       }
     };
+    // (every bulk-group operation of a warp - store, commit, wait - is issued under elect.sync, i.e. by the same
+    // elected lane, and the compiler keeps the TMA operands in uniform registers)
     auto stage_reuse = [&]() {  // the previous chunk's stores must have read the staging tiles
-      if (lane == 0) tma_store_wait_read();
+      if (elect_one()) tma_store_wait_read();
       __syncwarp();
     };
     auto stage_flush = [&](const CUtensorMap* m, int tile, int x, int y) {
-      if (lane == 0) tma_store_2d(m, stage + tile * OUT_TILE_BYTES, x, y);
+      if (elect_one()) tma_store_2d(m, stage + tile * OUT_TILE_BYTES, x, y);
     };
     auto stage_commit = [&]() {
-      if (lane == 0) tma_store_commit();
+      if (elect_one()) tma_store_commit();
     };
     uint32_t ring_n = 0;
     auto ring_store = [&](const CUtensorMap* m, const float* v32, int x, int y) {
       const int tile = ring_n % TILES;
       ++ring_n;
-      if (lane == 0) tma_store_wait_read_pending<(TILES > 1 ? TILES - 1 : 0)>();
+      if (elect_one()) tma_store_wait_read_pending<(TILES > 1 ? TILES - 1 : 0)>();
       __syncwarp();
       stage_write(tile, v32);
       fence_proxy_async_smem();
@@ -471,7 +476,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     };
     if (EPI == B200_EPI_GEGLU_BWD || EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) {
       GemmUnit u0;   // the first chunk of the CTA's first unit is requested before the loop
-      if (gemm_unit(g, 0, u0) && lane == 0) {
+      if (gemm_unit(g, 0, u0) && elect_one()) {
         const int x0 = u0.n_blk * g.tile_n_step + cpart * NCH * 32;
         if (x0 < g.N) {
           if (EPI == B200_EPI_RESID || EPI == EPI_RESID_DEEP) res_load(0, x0, u0.m_blk * BM + q * 32);
@@ -546,7 +551,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
           if (have && ncol < g.N) {
             stage_reuse();   // the stores that last read that set are done with it
-            if (lane == 0) aux_load(aux_n % NSETS, ncol, ny);   // (aux_n already counts the current chunk)
+            if (elect_one()) aux_load(aux_n % NSETS, ncol, ny);   // (aux_n already counts the current chunk)
           }
         };
 #pragma unroll 1
@@ -644,7 +649,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if (have && ncol < g.N) {
               stage_reuse();
-              if (lane == 0) res_load(0, ncol, ny);
+              if (elect_one()) res_load(0, ncol, ny);
             }
           }
         }
@@ -670,7 +675,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
             if (have && ncol < g.N) {
               stage_reuse();
-              if (lane == 0) res_load((aux_n + 1) & 1, ncol, ny);
+              if (elect_one()) res_load((aux_n + 1) & 1, ncol, ny);
             }
           }
           if (col >= g.N) continue;  // warp-uniform (never prefetched either)
@@ -792,7 +797,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
-    if (lane == 0) tma_store_wait_all();  // staged stores must finish before the CTA's smem goes away
+    if (elect_one()) tma_store_wait_all();  // staged stores must finish before the CTA's smem goes away
   }
 
   tc_fence_before();

@@ -32,6 +32,55 @@ def test_attn_fwd(cfg_name, attn_type):
     err = (out.float() - ref_o).abs().max().item()
     assert err < 2e-2, f"o err {err}"
     assert (lse - ref_l).abs().max().item() < 2e-2
+    _assert_close_elementwise(out.float(), ref_o, "o")
+
+
+@pytest.mark.parametrize("attn_type", ["axial_row", "axial_col"])
+def test_attn_fwd_many_items(attn_type):
+    """Batch 12 at TTT shapes: every persistent CTA of the pipelined forward walks several (batch, head) items, so
+    the hand-over of the resident text keys/values between items and the wrap of the query ring are exercised."""
+    cfg = ttt_config()
+    B = 12
+    M = B * cfg.seq_len
+    qkv = _qkv(cfg, B, seed=7)
+    out = torch.zeros(M, cfg.inner_dim, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(B, cfg.heads, cfg.seq_len, device="cuda")
+    for _ in range(2):
+        A.attn_fwd(qkv, out, lse, cfg, attn_type)
+    torch.cuda.synchronize()
+    for b0 in range(0, B, 4):
+        sl = slice(b0 * cfg.seq_len, (b0 + 4) * cfg.seq_len)
+        ref_o, ref_l = A.attn_core_ref(qkv[sl], cfg, attn_type)
+        assert (lse[b0:b0 + 4] - ref_l).abs().max().item() < 2e-2
+        _assert_close_elementwise(out[sl].float(), ref_o, f"o[{b0}:{b0 + 4}]")
+
+
+def _assert_close_elementwise(got, ref, name, rtol=2e-2, atol=4e-3):
+    """Per-element check (a max-error-over-max-magnitude bound would let a wrong small-magnitude region pass)."""
+    bad = (got - ref).abs() > atol + rtol * ref.abs()
+    assert not bad.any(), f"{name}: {int(bad.sum())} of {bad.numel()} elements off; worst {(got - ref).abs().max().item()}"
+    cos = torch.nn.functional.cosine_similarity(got.flatten(), ref.flatten(), dim=0).item()
+    assert cos > 0.9995, f"{name}: cosine {cos}"
+
+
+@pytest.mark.parametrize("attn_type", ["axial_row", "axial_col"])
+@pytest.mark.parametrize("B", [1, 3])
+def test_attn_fwd_rising_scores(attn_type, B):
+    """Keys grow in magnitude along the sequence, so later score chunks exceed the running maximum by far more than
+    the 2^8 slack of the pipelined forward: exercises its in-TMEM rescale of the output accumulator."""
+    cfg = ttt_config()
+    M = B * cfg.seq_len
+    qkv = _qkv(cfg, B, seed=5)
+    pos = torch.arange(M, device="cuda") % cfg.seq_len
+    scale = torch.where(pos < 128, 1.0, torch.where(pos < cfg.text_len, 4.0, 9.0)).to(torch.bfloat16)
+    qkv[:M, cfg.inner_dim: 2 * cfg.inner_dim] *= scale[:, None]
+    out = torch.zeros(M, cfg.inner_dim, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(B, cfg.heads, cfg.seq_len, device="cuda")
+    A.attn_fwd(qkv, out, lse, cfg, attn_type)
+    torch.cuda.synchronize()
+    ref_o, ref_l = A.attn_core_ref(qkv[:M], cfg, attn_type)
+    assert (lse - ref_l).abs().max().item() < 3e-2
+    _assert_close_elementwise(out.float(), ref_o, "o", rtol=3e-2, atol=8e-3)
 
 
 @pytest.mark.parametrize("cfg_name", ["small", "ttt"])
