@@ -22,6 +22,9 @@ int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t*
                       const uint32_t* box);
 int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
                    CUtensorMap* taux);
+int attn4_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta, void* dqkv,
+              float* kv_acc, const void* rot, const void* rot_t, float q_scale, int B, int H, int seq, int T, int F, int mode,
+              cudaStream_t st);
 
 constexpr int ATTB_THREADS = 320;   // TMA warp, MMA warp, 8 worker warps
 
@@ -486,6 +489,13 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = conv_kernel / 2;
   if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // text + axial patterns: the fourth-generation kernels (attn_bwd4_sm100.cu); DALLE_B200_ATTN_BWD=2 keeps this file's
+  // kernel for A/B runs
+  static const int which = [] { const char* e = getenv("DALLE_B200_ATTN_BWD"); return e ? atoi(e) : 4; }();
+  if (which == 4) {
+    const int rc4 = attn4_bwd(qkv, out, d_out, lse, delta, dqkv, kv_acc, rot, rot_t, q_scale, B, H, seq, T, F, mode, st);
+    if (rc4 <= 0) return rc4;
+  }
   const int HD = H * 64;
   AttnBwdArgs a;
   a.g = g; a.lse = lse; a.out = reinterpret_cast<const __nv_bfloat16*>(out); (void)delta; a.dqkv = reinterpret_cast<__nv_bfloat16*>(dqkv); a.kv_acc = kv_acc;

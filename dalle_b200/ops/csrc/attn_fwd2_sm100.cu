@@ -20,6 +20,7 @@ namespace b200 {
 int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
                    CUtensorMap* taux);
 int attn3_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode, cudaStream_t st);
+int attn4_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode, cudaStream_t st);
 
 constexpr int AF2_THREADS = 128;
 constexpr int AF2_MAXK = 144;                       // keys per chunk
@@ -217,12 +218,14 @@ extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int 
   // wider grids take the first-generation kernel, which keeps whole score rows in TMEM
   if (32 % F) return b200_attn_fwd_v1(qkv, out, lse, B, H, seq, T, F, mode, conv_kernel, stream);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  // DALLE_B200_ATTN_V3=1 routes text + axial patterns to the persistent pipelined kernel (attn3_fwd_sm100.cu): correct
-  // (same tests), but at the benchmark shapes still slower than this one (370 vs 265 us at batch 32) - its timeline
-  // and the MMA-latency probe are in profiles/attn3_fwd_timeline_r2.txt
-  static const bool v3 = getenv("DALLE_B200_ATTN_V3") != nullptr;
-  if (v3) {
-    const int rc3 = attn3_fwd(qkv, out, lse, B, H, seq, T, F, mode, st);
+  // text + axial patterns have three forward kernels; DALLE_B200_ATTN_FWD = 2 | 3 | 4 picks one for A/B runs:
+  //   4  (default) many light CTAs, 64-key chunks, P and O in TMEM (attn_fwd4_sm100.cu)
+  //   3  persistent software-pipelined kernel (attn3_fwd_sm100.cu; slower, see profiles/attn3_fwd_timeline_r2.txt)
+  //   2  this file
+  static const int which = [] { const char* e = getenv("DALLE_B200_ATTN_FWD"); return e ? atoi(e) : 4; }();
+  if (which == 3 || which == 4) {
+    const int rc3 = which == 3 ? attn3_fwd(qkv, out, lse, B, H, seq, T, F, mode, st)
+                               : attn4_fwd(qkv, out, lse, B, H, seq, T, F, mode, st);
     if (rc3 <= 0) return rc3;
   }
   AttnFwd2Args a;

@@ -111,3 +111,8 @@ def test_attn_bwd(cfg_name, attn_type):
         err = (dqkv[:, sl].float() - ref[:, sl]).abs().max().item()
         den = ref[:, sl].abs().max().item()
         assert err / den < 3e-2, f"{name}: err {err} / {den}"
+        cos = torch.nn.functional.cosine_similarity(dqkv[:, sl].float().flatten(), ref[:, sl].flatten(), dim=0).item()
+        assert cos > 0.999, f"{name}: cosine {cos}"
+        # per row: a wrong small-magnitude region (one token's gradient) must not hide behind the global maximum
+        rerr = (dqkv[:, sl].float() - ref[:, sl]).norm(dim=1) / (ref[:, sl].norm(dim=1) + 1e-3 * den)
+        assert rerr.max().item() < 6e-2, f"{name}: worst row relative error {rerr.max().item()} at row {int(rerr.argmax())}"
