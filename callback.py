@@ -41,7 +41,10 @@ class CollaborativeCallback:
 
     def on_step_end(self, *unused, loss: Optional[float] = None, **kwargs):
         opt = self.collaborative_optimizer
-        if not self.params_are_finite():
+        ok = self.params_are_finite()
+        if hasattr(opt, "all_ranks_agree"):   # a multi-GPU peer rolls back as one: every rank or none
+            ok = opt.all_ranks_agree(ok)
+        if not ok:
             if not os.path.exists(self.state_path):
                 raise RuntimeError("Encountered broken parameters, but there is no backup to fall back to.")
             logger.warning("Parameters are invalid, reloading model from earlier state")
@@ -62,7 +65,7 @@ class CollaborativeCallback:
                 if self.steps:
                     logger.info(f"Local loss: {self.loss / self.steps}")
                 self.loss, self.steps = 0.0, 0
-                if opt.local_epoch == opt.tracker.global_epoch:
+                if opt.local_epoch == opt.tracker.global_epoch and self.dht is not None:
                     self.dht.store(key=opt.run_id + "_metrics", subkey=self.task.local_public_key,
                                    value=record.dict(), expiration_time=get_dht_time() + self.statistics_expiration,
                                    return_future=True)
@@ -82,11 +85,18 @@ class CollaborativeCallback:
 
     @torch.no_grad()
     def backup_state(self) -> Any:
-        logger.info("Saving backup")
         opt = self.collaborative_optimizer
-        return torch.save({"model": self.task.model.state_dict(), "training": opt.state_dict(),
-                           "scheduler": opt.state_averager.scheduler.state_dict(), "local_epoch": opt.local_epoch},
-                          self.state_path)
+        # (in a multi-GPU peer state_dict() is collective - it gathers the sharded optimizer state - and the leader
+        # rank writes the file)
+        state = {"model": self.task.model.state_dict(), "training": opt.state_dict(),
+                 "scheduler": opt.state_averager.scheduler.state_dict(), "local_epoch": opt.local_epoch}
+        if not getattr(opt, "is_leader", True):
+            return None
+        logger.info("Saving backup")
+        tmp = f"{self.state_path}.tmp{os.getpid()}"
+        torch.save(state, tmp)
+        os.replace(tmp, self.state_path)   # readers (other ranks restoring after a NaN) never see a partial file
+        return None
 
     @torch.no_grad()
     def restore_from_backup(self, path, check_step: bool = False):

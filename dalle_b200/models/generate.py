@@ -8,8 +8,9 @@ Two executors with identical semantics:
 * the GPU path (``DecodeEngine`` in models/decode_engine.py) - the same step as sm_100a kernels captured in a CUDA
   graph; used automatically for CUDA tensors when ``dim_head == 64``.
 
-Sampling: logits of the last position -> (image segment only) -> temperature -> top-k (if > 0) -> nucleus top-p
-(if < 1) -> multinomial draw.
+Sampling: logits of the last position -> (image segment only) -> top-k (if > 0) -> nucleus top-p (if < 1), both on
+the raw logits -> divide the kept logits by the temperature -> multinomial draw (dalle-pytorch's order; the CUDA
+sampler in ops/csrc/decode.cu does the same).
 """
 from __future__ import annotations
 

@@ -244,7 +244,9 @@ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
 }
 
 // One block (1024 threads) per sample: sort the n (<= 8192) logits descending (bitonic, in shared memory),
-// cut by top-k / top-p, draw one token.  Writes ids[b, pos + 1] = token + id_offset and codes[b, pos + 1 - T].
+// cut by top-k / top-p on the RAW logits (temperature 1), then draw one token from the kept set at the given
+// temperature - the order of dalle-pytorch's generate_images and of models/generate.py:sample_from_logits
+// (filter, then divide by the temperature).  Writes ids[b, pos + 1] = token + id_offset and codes[b, pos + 1 - T].
 constexpr int SAMPLE_MAX = 8192;
 __global__ void __launch_bounds__(1024)
 decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, float inv_temperature, int top_k,
@@ -261,7 +263,7 @@ decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, fl
   for (int i = tid; i < npow; i += blockDim.x) {
     unsigned long long key = 0ull;  // sorts last
     if (i < n) {
-      const float x = __bfloat162float(row[i]) * inv_temperature;
+      const float x = __bfloat162float(row[i]);   // the order is the same at any temperature > 0
       uint32_t u = __float_as_uint(x);
       u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);  // monotone map float -> uint
       key = (static_cast<unsigned long long>(u) << 32) | (0xffffffffu - static_cast<uint32_t>(i));
@@ -296,7 +298,7 @@ decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, fl
   __shared__ int smin[2];
   const int per = (npow + blockDim.x - 1) / blockDim.x;   // <= 8
   const int i0 = tid * per;
-  float e[8];
+  float e[8];    // unnormalised probabilities at temperature 1 (nucleus cut), then at the sampling temperature (draw)
   float local = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
@@ -347,11 +349,14 @@ decode_sample_kernel(const __nv_bfloat16* __restrict__ logits, int ld, int n, fl
   }
   __syncthreads();
   const int cut = max(smin[0], 1);
-  // mass of the kept prefix, then the draw
+  // mass of the kept prefix at the sampling temperature, then the draw
   float kl = 0.f;
 #pragma unroll
-  for (int k = 0; k < 8; ++k)
-    if (k < per && i0 + k < cut) kl += e[k];
+  for (int k = 0; k < 8; ++k) {
+    const int i = i0 + k;
+    e[k] = (k < per && i < cut) ? __expf((val(i) - mx) * inv_temperature) : 0.f;
+    kl += e[k];
+  }
   float kept;
   const float koff = block_exclusive(kl, kept);
   const unsigned long long seed = *seed_ptr;

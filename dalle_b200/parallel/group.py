@@ -77,23 +77,10 @@ class FusedGroupAverager:
         ``grad_scale * sum_r grad_r`` (reduce-scatter + all-gather over NVLink, same kernel, no optimizer work)."""
         d = self._desc
         d.grad_scale, d.zero_grad, d.epoch, d.reduce_only = grad_scale, 0, self.epoch, 1
-        self.epoch = (self.epoch + 4) & 0x7FFFFFFF
+        self.epoch = (self.epoch + 4) & 0xFFFFFFFF   # wraps like the device's 32-bit signed-difference compare
         rc = lib.cuda_lib().b200_group_lamb_step(ctypes.byref(d), torch.cuda.current_stream().cuda_stream)
         lib.check(rc, "b200_group_lamb_step(reduce_only)")
         d.reduce_only = 0
-
-    @torch.no_grad()
-    def gather_full_state(self):
-        """Full (unsharded) copies of the optimizer state on every rank: each rank only ever writes its own shard,
-        the rest stays zero, so a SUM all-reduce of copies assembles the state (NCCL; rare: checkpoints / donors)."""
-        f = self.opt._fused
-        out = {}
-        for name in ("q1", "q2", "f1", "f2", "absmax1", "absmax2"):
-            t = getattr(f, name).clone()
-            t32 = t.to(torch.int32) if t.dtype == torch.uint8 else t
-            dist.all_reduce(t32, group=self.pg)
-            out[name] = t32.to(t.dtype)
-        return out
 
     def step(self, grad_scale: float = 1.0, zero_grad: bool = True):
         opt, d = self.opt, self._desc
@@ -101,7 +88,7 @@ class FusedGroupAverager:
         d.beta1, d.beta2, d.eps = g0["betas"][0], g0["betas"][1], g0["eps"]
         d.max_grad_norm, d.clamp_value, d.lr = float(opt.max_grad_norm or 0.0), opt.clamp_value, g0["lr"]
         d.grad_scale, d.zero_grad, d.epoch = grad_scale, int(zero_grad), self.epoch
-        self.epoch = (self.epoch + 4) & 0x7FFFFFFF
+        self.epoch = (self.epoch + 4) & 0xFFFFFFFF   # wraps like the device's 32-bit signed-difference compare
         rc = lib.cuda_lib().b200_group_lamb_step(ctypes.byref(d), torch.cuda.current_stream().cuda_stream)
         lib.check(rc, "b200_group_lamb_step")
         opt._fused.layout.mark_shadows_fresh()

@@ -50,6 +50,22 @@ def grads_are_finite(model) -> bool:
     return all(p.grad is None or bool(torch.isfinite(p.grad).all()) for p in model.parameters())
 
 
+def _failpoint_nan(model, micro: int):
+    """Fault injection: ``DALLE_B200_INJECT_NAN="<rank>:<micro step>"`` poisons one parameter of that
+    rank after that micro-step, so tests can watch the NaN guard roll the peer (all ranks of a group) back."""
+    import os
+
+    spec = os.environ.get("DALLE_B200_INJECT_NAN")
+    if not spec:
+        return
+    rank_s, step_s = spec.split(":")
+    my_rank = int(os.environ.get("RANK", "0"))
+    if int(rank_s) == my_rank and int(step_s) == micro:
+        with torch.no_grad():
+            next(model.parameters()).view(-1)[0] = float("nan")
+        logger.warning(f"failpoint: injected NaN into the parameters of rank {my_rank} after micro-step {micro}")
+
+
 class CollaborativeTrainer:
     def __init__(self, *, model, args, data_collator, train_dataset, collaborative_optimizer, callbacks=(),
                  data_seed: int = 0, max_micro_steps: Optional[int] = None, check_finite_every_step: bool = True):
@@ -79,7 +95,10 @@ class CollaborativeTrainer:
             (loss / accum).backward()
             micro += 1
             if micro % accum == 0:
-                if self.check_finite and not grads_are_finite(self.model):
+                finite = (not self.check_finite) or grads_are_finite(self.model)
+                if self.check_finite and hasattr(self.opt, "all_ranks_agree"):
+                    finite = self.opt.all_ranks_agree(finite)   # a multi-GPU peer drops a micro-batch on every rank or none
+                if not finite:
                     logger.warning("non-finite gradients: dropping this micro-batch")
                     for p in self.model.parameters():
                         if p.grad is not None:
@@ -96,6 +115,7 @@ class CollaborativeTrainer:
                     logger.info(f"step {micro // accum}: loss {loss_log / n:.4f}, lr {self.lr_scheduler.get_lr()[0]:.3g}, "
                                 f"{n * self.args.per_device_train_batch_size * accum / (time.time() - t_log):.1f} samples/s")
                     t_log, loss_log = time.time(), 0.0
+            _failpoint_nan(self.model, micro)
             if self.max_micro_steps is not None and micro >= self.max_micro_steps:
                 break
             if micro >= self.args.max_steps * accum:

@@ -19,7 +19,7 @@ import sys
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-STATE = os.path.join(ROOT, ".swarm.json")
+STATE = os.path.join(os.environ.get("DALLE_B200_SWARM_STATE_DIR", os.path.expanduser("~")), ".dalle_b200_swarm.json")
 
 
 def _wait_for_maddr(log_path, timeout=120.0):
@@ -49,11 +49,17 @@ def create(a, extra):
                "--assist_in_averaging", "true" if a.aux_assists else "false"]
     procs.append(subprocess.Popen(aux_cmd, stdout=open(aux_log, "w"), stderr=subprocess.STDOUT, env=env, cwd=a.workdir))
     maddr = _wait_for_maddr(aux_log)
+    R = max(1, a.ranks_per_peer)
     for i in range(a.peers):
         penv = dict(env)
         if a.device == "cuda":
-            penv["CUDA_VISIBLE_DEVICES"] = str(i % max(1, a.gpus))
-        cmd = [sys.executable, os.path.join(ROOT, "run_trainer.py"), *common, "--initial_peers", maddr,
+            first = (i * R) % max(1, a.gpus)
+            penv["CUDA_VISIBLE_DEVICES"] = ",".join(str((first + r) % max(1, a.gpus)) for r in range(R))
+        # a peer of several ranks is one torchrun launch: the ranks form ONE swarm peer (NVLink-fused averaging inside)
+        launcher = [sys.executable] if R == 1 else [
+            sys.executable, "-m", "torch.distributed.run", "--nnodes", "1", "--nproc-per-node", str(R),
+            "--master-addr", "127.0.0.1", "--master-port", str(a.base_port + i)]
+        cmd = [*launcher, os.path.join(ROOT, "run_trainer.py"), *common, "--initial_peers", maddr,
                "--host_maddrs", "/ip4/127.0.0.1/tcp/0", "--synthetic_data", "true",
                "--per_device_train_batch_size", str(a.batch), "--gradient_accumulation_steps", "1",
                "--output_dir", os.path.join(a.workdir, f"peer{i}_out"),
@@ -97,6 +103,9 @@ def main(argv=None):
     ap.add_argument("--peers", type=int, default=4, help="trainer peers (reference SWARM_SIZE = 4)")
     ap.add_argument("--device", choices=["cpu", "cuda"], default="cuda")
     ap.add_argument("--gpus", type=int, default=8)
+    ap.add_argument("--ranks_per_peer", type=int, default=1,
+                    help="GPUs (processes) per trainer peer; > 1 launches each peer under torchrun as one group")
+    ap.add_argument("--base_port", type=int, default=29700, help="torchrun rendezvous port of peer i = base_port + i")
     ap.add_argument("--prefix", default="my-model")
     ap.add_argument("--model_preset", default="ttt")
     ap.add_argument("--batch", type=int, default=1, help="per-device micro-batch (reference cloud workers use 1)")

@@ -37,12 +37,23 @@ class VQGanParams:
         self.num_layers, self.image_size, self.num_tokens, self.is_gumbel = num_layers, image_size, num_tokens, is_gumbel
 
 
+def group_rank_world():
+    """(rank, world) of the multi-GPU peer this process belongs to: a torchrun launch is ONE swarm peer made of one
+    process per GPU; a plain ``python run_trainer.py`` is a peer of its own, (0, 1)."""
+    import torch.distributed as dist
+
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
 class TrainingTask:
     _authorizer = _dht = _collaborative_optimizer = _training_dataset = None
 
     def __init__(self, peer_args: BasePeerArguments, trainer_args: HFTrainerArguments,
                  collab_args: CollaborativeArguments):
         self.peer_args, self.trainer_args, self.collab_args = peer_args, trainer_args, collab_args
+        self.group_rank, self.group_world = group_rank_world()
         # the reference dereferences authorizer.username unconditionally and crashes with --authorize false
         auth = self.authorizer
         self.trainer_args.run_name = auth.username if auth is not None else (
@@ -83,6 +94,8 @@ class TrainingTask:
 
     @property
     def dht(self) -> DHT:
+        if self.group_rank != 0:
+            return None   # inside a multi-GPU peer only the leader rank talks to the swarm
         if self._dht is None:
             a = self.peer_args
             self._dht = DHT(start=True, initial_peers=a.initial_peers, client_mode=a.client_mode,
@@ -101,6 +114,21 @@ class TrainingTask:
             params, make_opt, make_sched = self._get_local_optimizer_and_scheduler(self.trainer_args)
             compression = SizeAdaptiveCompression(threshold=2 ** 16 + 1, less=Float16Compression(),
                                                   greater_equal=Uniform8BitQuantization())
+            if self.group_world > 1:
+                # one swarm peer = all ranks of this torchrun launch: NVLink-fused averaging + sharded LAMB inside the
+                # group, the leader rank on the swarm's TCP plane (dalle_b200/collab/group_optimizer.py)
+                from dalle_b200.collab.group_optimizer import GroupOptimizer
+
+                a = self.trainer_args
+                per_rank = a.per_device_train_batch_size * a.gradient_accumulation_steps
+                self._collaborative_optimizer = GroupOptimizer(
+                    dht=self.dht, run_id=self.peer_args.experiment_prefix, params=params, optimizer=make_opt,
+                    scheduler=make_sched, delay_optimizer_step=True, batch_size_per_step=per_rank * self.group_world,
+                    grad_compression=compression, state_averaging_compression=compression,
+                    client_mode=self.peer_args.client_mode, verbose=True,
+                    target_group_size=int(os.environ.get("DALLE_B200_TARGET_GROUP_SIZE", "0")) or None,
+                    **asdict(self.collab_args))
+                return self._collaborative_optimizer
             self._collaborative_optimizer = Optimizer(
                 dht=self.dht, run_id=self.peer_args.experiment_prefix, params=params, optimizer=make_opt,
                 scheduler=make_sched, offload_optimizer=True, delay_grad_averaging=False, delay_optimizer_step=True,
@@ -122,6 +150,7 @@ class TrainingTask:
     def training_dataset(self):
         if self._training_dataset is None:
             # deterministic per-peer shuffle seed (the reference's hash(bytes) is salted per process)
+            # (inside a multi-GPU peer every rank has its own key, hence its own order)
             seed = int.from_bytes(hashlib.sha256(self.local_public_key).digest()[:4], "little") % 2 ** 31
             cfg = self.model.model.cfg
             self._training_dataset = make_dataset(

@@ -67,3 +67,29 @@ def test_sampler_distribution():
                               pos.data_ptr(), 1, trials, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     assert (codes[:, 0] == 7).all()
+
+
+@pytest.mark.parametrize("temperature", [0.5, 1.0, 2.0])
+@pytest.mark.parametrize("top_p", [0.5, 0.9, 1.0])
+def test_sampler_filters_then_applies_temperature(temperature, top_p):
+    """The kept set comes from the raw logits (temperature 1), the draw from the kept set at `temperature`: the order
+    of models/generate.py:sample_from_logits and of dalle-pytorch's generate_images."""
+    from dalle_b200.ops import lib
+
+    n, trials = 512, 6000
+    g = torch.Generator().manual_seed(3)
+    row = (torch.randn(n, generator=g) * 1.5).to(torch.bfloat16)
+    logits = row.cuda().repeat(trials, 1).contiguous()
+    want = (G.filter_logits(row.float()[None], 0, top_p) / temperature).softmax(-1)[0]
+    ids = torch.zeros(trials, 8, dtype=torch.int64, device="cuda")
+    codes = torch.zeros(trials, 8, dtype=torch.int64, device="cuda")
+    pos = torch.zeros(1, dtype=torch.int32, device="cuda")
+    seed = torch.tensor([99], dtype=torch.int64, device="cuda")
+    rc = lib.cuda_lib().b200_decode_sample(logits.data_ptr(), n, n, temperature, 0, top_p, seed.data_ptr(), ids.data_ptr(), 8, 0,
+                                           codes.data_ptr(), 8, pos.data_ptr(), 1, trials,
+                                           torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    torch.cuda.synchronize()
+    freq = torch.bincount(codes[:, 0].cpu(), minlength=n).float() / trials
+    assert freq[want == 0].sum().item() == 0.0, "drew a token outside the nucleus of the raw logits"
+    assert (freq - want).abs().max().item() < 0.03
