@@ -33,7 +33,11 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "eager"])
+    ap.add_argument("--checkpoint", action="store_true", help="eager arm: checkpoint every layer")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "eager", "naive"],
+                    help="b200: this framework; reference: the unmodified reference (not installable offline); eager: baseline "
+                         "B1 = the same model on cuBLAS / SDPA / DDP-NCCL / foreach-LAMB (dalle_b200/baseline_ddp.py); naive: "
+                         "the fp32-oracle model run in bf16 with per-tensor all-reduce (the slow stand-in of round 1)")
     ap.add_argument("--batch", type=int, default=32, help="micro-batch per GPU")
     ap.add_argument("--preset", default="ttt")
     ap.add_argument("--averaging", default="auto", choices=["auto", "fused", "nccl"])
@@ -144,10 +148,39 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    if args.impl == "eager":
+    baseline_note = None
+    if args.impl == "naive":
         from dalle_b200.baseline_eager import EagerTrainer
 
         trainer = EagerTrainer(cfg, dev)
+    elif args.impl == "eager":
+        from dalle_b200.baseline_ddp import DDPTrainer
+
+        # store every activation if the batch fits (what the product does); otherwise checkpoint per layer
+        def build(ckpt):
+            return DDPTrainer(cfg, dev, use_checkpoint=ckpt)
+
+        trainer = build(args.checkpoint)
+        if not args.checkpoint:
+            g0 = torch.Generator().manual_seed(7)
+            tt = torch.randint(1, cfg.num_text_tokens, (B, cfg.text_seq_len), generator=g0).to(dev)
+            ti = torch.randint(0, cfg.num_image_tokens, (B, cfg.image_seq_len), generator=g0).to(dev)
+            fits = torch.ones(1, device=dev)
+            try:
+                trainer.step(tt, ti)
+            except torch.cuda.OutOfMemoryError:
+                fits.zero_()
+            if world > 1:
+                dist.all_reduce(fits, op=dist.ReduceOp.MIN)
+            if fits.item() == 0:
+                del trainer
+                import gc
+
+                gc.collect()
+                torch.cuda.empty_cache()
+                trainer = build(True)
+        baseline_note = ("activations stored by autograd" if not trainer.net.use_checkpoint
+                         else "per-layer activation checkpointing (the stored-activation graph does not fit at this batch)")
     else:
         trainer = GroupTrainer(cfg, dev, averaging=args.averaging, seed=0, payload=args.payload)
 
@@ -227,10 +260,12 @@ def main():
             "config": {"model": "TTT DALL-E dim1024 depth64 heads16 shared-attn/ff axial_row/col+conv_like, "
                                 "256 text + 1024 image tokens, vocab 8192" if args.preset == "ttt" else args.preset,
                        "global_batch": B * world, "micro_batch_per_gpu": B, "seq_len": cfg.seq_len,
-                       "parallelism": f"dp{world}", "optimizer": "LAMB-8bit, one update per step",
+                       "parallelism": f"dp{world}",
+                       "optimizer": "LAMB (fp32 moments, torch._foreach), one update per step" if args.impl == "eager"
+                       else "LAMB-8bit, one update per step",
                        "averaging": getattr(trainer, "averaging", "n/a"),
                        "averaging_payload": getattr(trainer, "payload", "n/a"),
-                       "activations": activation_policy(trainer, B, cfg),
+                       "activations": baseline_note or activation_policy(trainer, B, cfg),
                        "l2": "per-step working set (>5 GB activations/weights) exceeds the 126 MB L2; no flush"},
             "exposed_averaging_ms_per_step": exposed_ms,
             "exposed_averaging_share": (exposed_ms / (ms_total / K)) if exposed_ms else None,

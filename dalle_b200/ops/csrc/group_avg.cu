@@ -23,14 +23,28 @@
 // st.release.sys / ld.acquire.sys, bracketed by grid syncs.  Spins are bounded (trap instead of hanging the box).
 #include <cooperative_groups.h>
 
+#include <cstdlib>
+
 #include "b200_api.h"
 #include "lamb_device.cuh"
+
+#include <cuda_fp16.h>
 
 namespace cg = cooperative_groups;
 
 namespace b200 {
 
 constexpr int MAX_RANKS = 8;
+// hivemind's averaging codecs on the NVLink hop (reference task.py:124-126): a CHUNK is 32
+// consecutive 4096-element blocks = 131072 elements = the 512 KiB part hivemind serialises at a time.
+//   CODEC_FP16  clamp to +-65504, fp16                                    (tensors below 65537 elements)
+//   CODEC_U8H   mu, sigma over the chunk; 256 uniform bins over 6 sigma; a 256-entry codebook of bucket MEANS
+//               (of the original values) travels with the codes              (tensors of 65537 elements and more)
+// The payload buffer has 2 bytes per element: an fp16 chunk fills its 256 KiB, a U8H chunk uses 1 byte per element of
+// codes followed by the 1 KiB codebook.
+constexpr int CHUNK_BLOCKS = 32;
+constexpr int CODEC_FP16 = 3, CODEC_U8H = 4;
+constexpr long long CHUNK_BYTES = 2ll * CHUNK_BLOCKS * 4096;
 
 struct GroupArgs {
   int rank, world;
@@ -45,10 +59,13 @@ struct GroupArgs {
   int n_blocks;                       // total blocks of the flat buffer
   int blk0, blk1;                     // my shard
   uint32_t epoch;                     // barrier values epoch+1 .. epoch+4 are used by this launch
-  int payload_mode;                   // 0 = fp32 P2P loads, 1 = bf16 payload, 2 = uniform 8-bit payload
-                                      //     (int8 codes + one fp32 scale per 4096-element block)
+  int payload_mode;                   // 0 = fp32 P2P loads, 1 = bf16 payload, 2 = absmax int8 payload (int8 codes + one
+                                      //     fp32 scale per 4096-element block), 3 = hivemind's codecs, chosen per chunk
+                                      //     of 32 blocks by `chunk_codec` (CODEC_FP16 / CODEC_U8H)
+  const uint8_t* chunk_codec;         // [ceil(n_blocks / 32)], payload mode 3
   int zero_grad;
   int reduce_only;                    // 1: stop after the reduce phase and give EVERY rank the reduced gradient
+  int spin_limit_s;                   // cross-rank barrier: seconds before a missing peer turns into a trap
   // local optimizer state (shard only is touched)
   uint8_t* q1; uint8_t* q2; float* f1; float* f2; float* absmax1; float* absmax2;
   const float* code1; const float* code2;
@@ -75,9 +92,14 @@ __device__ void rank_barrier(const GroupArgs& a, uint32_t value, cg::grid_group&
   if (blockIdx.x == 0 && threadIdx.x < a.world) {
     st_release_sys(a.sig[threadIdx.x] + a.rank, value);
     const uint32_t* mine = a.sig[a.rank] + threadIdx.x;
-    const long long t0 = clock64();
+    // a peer may legitimately be late by a long time (data-loader stall, checkpoint write, first-call JIT of another
+    // rank): the spin is bounded only to turn a dead peer into a launch failure - a.spin_limit_s seconds, 600 by
+    // default (DALLE_B200_GROUP_TIMEOUT_S); NCCL would wait forever here
+    const uint64_t t0 = global_timer_ns();
+    const uint64_t limit = static_cast<uint64_t>(a.spin_limit_s) * 1000000000ull;
+    uint32_t polls = 0;
     while (static_cast<int32_t>(ld_acquire_sys(mine) - value) < 0) {
-      if (clock64() - t0 > 20000000000LL) __trap();
+      if ((++polls & 0xFFFFu) == 0 && global_timer_ns() - t0 > limit) __trap();
     }
   }
   grid.sync();
@@ -86,7 +108,7 @@ __device__ void rank_barrier(const GroupArgs& a, uint32_t value, cg::grid_group&
 __global__ void __launch_bounds__(LAMB_THREADS)
 group_lamb_kernel(const GroupArgs a) {
   cg::grid_group grid = cg::this_grid();
-  __shared__ float sc1[256], sc2[256], sred[8];
+  __shared__ float sc1[256], sc2[256], sred[8], s_book[256];
   sc1[threadIdx.x] = a.code1[threadIdx.x];
   sc2[threadIdx.x] = a.code2[threadIdx.x];
   const int e0 = threadIdx.x * EPT;
@@ -140,6 +162,79 @@ group_lamb_kernel(const GroupArgs a) {
       if (threadIdx.x == 0) steps[b] = isfinite(am) ? step : am;
     }
   }
+  if (a.payload_mode == 3) {
+    // my gradients -> hivemind payload, one CTA per chunk
+    __shared__ float h_sum[256];
+    __shared__ int h_cnt[256];
+    const int n_chunks = (a.n_blocks + CHUNK_BLOCKS - 1) / CHUNK_BLOCKS;
+    uint8_t* pay = reinterpret_cast<uint8_t*>(a.payload[a.rank]);
+    for (int ck = blockIdx.x; ck < n_chunks; ck += gridDim.x) {
+      const int b0 = ck * CHUNK_BLOCKS, b1 = min(b0 + CHUNK_BLOCKS, a.n_blocks);
+      const float* src = a.grad[a.rank] + static_cast<long long>(b0) * QBLOCK;
+      uint8_t* dst = pay + static_cast<long long>(ck) * CHUNK_BYTES;
+      if (a.chunk_codec[ck] == CODEC_FP16) {
+        for (int b = b0; b < b1; ++b) {
+          const float* s16 = src + static_cast<long long>(b - b0) * QBLOCK + e0;
+          uint32_t o[EPT / 2];
+#pragma unroll
+          for (int j = 0; j < EPT; j += 2) {
+            const __half2 hv = __floats2half2_rn(fminf(fmaxf(s16[j], -65504.f), 65504.f),
+                                                 fminf(fmaxf(s16[j + 1], -65504.f), 65504.f));
+            o[j / 2] = *reinterpret_cast<const uint32_t*>(&hv);
+          }
+          uint4* d4 = reinterpret_cast<uint4*>(dst + (static_cast<long long>(b - b0) * QBLOCK + e0) * 2);
+          d4[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          d4[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+        continue;
+      }
+      const float n_el = static_cast<float>(b1 - b0) * QBLOCK;
+      float sum = 0.f;
+      for (int b = b0; b < b1; ++b) {
+        const float* s16 = src + static_cast<long long>(b - b0) * QBLOCK + e0;
+#pragma unroll
+        for (int j = 0; j < EPT; ++j) sum += s16[j];
+      }
+      const float mu = block_sum(sum, sred) / n_el;
+      float ssq_c = 0.f;
+      for (int b = b0; b < b1; ++b) {
+        const float* s16 = src + static_cast<long long>(b - b0) * QBLOCK + e0;
+#pragma unroll
+        for (int j = 0; j < EPT; ++j) { const float c = s16[j] - mu; ssq_c += c * c; }
+      }
+      const float sigma = sqrtf(block_sum(ssq_c, sred) / fmaxf(n_el - 1.f, 1.f));
+      float scale = 6.0f * sigma / 256.0f;
+      const bool finite = isfinite(scale) && isfinite(mu);
+      if (!(scale > 0.f)) scale = 1.0f;
+      const float inv = 1.0f / scale;
+      h_sum[threadIdx.x] = 0.f;
+      h_cnt[threadIdx.x] = 0;
+      __syncthreads();
+      for (int b = b0; b < b1; ++b) {
+        const float* s16 = src + static_cast<long long>(b - b0) * QBLOCK + e0;
+        uint32_t o[EPT / 4];
+#pragma unroll
+        for (int j = 0; j < EPT; j += 4) {
+          uint32_t w = 0u;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float x = s16[j + e];
+            const int q = min(max(__float2int_rn((x - mu) * inv) + 128, 0), 255);   // round half to even
+            atomicAdd(&h_sum[q], x);
+            atomicAdd(&h_cnt[q], 1);
+            w |= static_cast<uint32_t>(q) << (8 * e);
+          }
+          o[j / 4] = w;
+        }
+        *reinterpret_cast<uint4*>(dst + static_cast<long long>(b - b0) * QBLOCK + e0) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+      __syncthreads();
+      // codebook = bucket means of the ORIGINAL values; a non-finite chunk stays visible as NaN to the reducer
+      float* book = reinterpret_cast<float*>(dst + static_cast<long long>(b1 - b0) * QBLOCK);   // right behind the codes
+      book[threadIdx.x] = finite ? h_sum[threadIdx.x] / static_cast<float>(max(h_cnt[threadIdx.x], 1)) : NAN;
+      __syncthreads();
+    }
+  }
   rank_barrier(a, a.epoch + 1, grid);  // phase 0: all gradients (and payloads) are complete
 
   // ---- phase 1: reduce-scatter into my shard -----------------------------------------------------
@@ -175,6 +270,33 @@ group_lamb_kernel(const GroupArgs a) {
           acc[j + 1] += step * static_cast<float>(static_cast<int8_t>((u >> 8) & 0xffu));
           acc[j + 2] += step * static_cast<float>(static_cast<int8_t>((u >> 16) & 0xffu));
           acc[j + 3] += step * static_cast<float>(static_cast<int8_t>(u >> 24));
+        }
+      } else if (a.payload_mode == 3) {
+        const int ck = b / CHUNK_BLOCKS;
+        const uint8_t* chunk = reinterpret_cast<const uint8_t*>(a.payload[src]) + static_cast<long long>(ck) * CHUNK_BYTES;
+        const long long off = static_cast<long long>(b - ck * CHUNK_BLOCKS) * QBLOCK + e0;
+        if (a.chunk_codec[ck] == CODEC_FP16) {
+          const uint4* p = reinterpret_cast<const uint4*>(chunk + off * 2);
+#pragma unroll
+          for (int j = 0; j < EPT; j += 8) {
+            const uint4 u = p[j / 8];
+            const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[e]));
+              acc[j + 2 * e] += f.x; acc[j + 2 * e + 1] += f.y;
+            }
+          }
+        } else {
+          // the peer's codebook of this chunk (1 KB over NVLink), then the block's codes
+          __syncthreads();
+          const int ck_blocks = min(CHUNK_BLOCKS, a.n_blocks - ck * CHUNK_BLOCKS);
+          s_book[threadIdx.x] = reinterpret_cast<const float*>(chunk + static_cast<long long>(ck_blocks) * QBLOCK)[threadIdx.x];
+          const uint4 u = *reinterpret_cast<const uint4*>(chunk + off);
+          __syncthreads();
+          const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+          for (int j = 0; j < EPT; ++j) acc[j] += s_book[(w[j >> 2] >> (8 * (j & 3))) & 0xffu];
         }
       } else {
         const float4* p = reinterpret_cast<const float4*>(a.grad[src] + base);
@@ -392,7 +514,13 @@ extern "C" int b200_group_lamb_step(const B200Group* d, void* stream) {
   }
   a.xstride = d->xstride; a.n_tensors = d->n_tensors; a.n_blocks = d->n_blocks;
   a.blk0 = d->blk0; a.blk1 = d->blk1; a.epoch = d->epoch; a.payload_mode = d->payload_mode; a.zero_grad = d->zero_grad;
+  a.chunk_codec = reinterpret_cast<const uint8_t*>(d->chunk_codec);
+  if (a.payload_mode == 3 && a.chunk_codec == nullptr) return -64;
   a.reduce_only = d->reduce_only;
+  {
+    static const int limit = [] { const char* e = getenv("DALLE_B200_GROUP_TIMEOUT_S"); const int v = e ? atoi(e) : 600; return v > 0 ? v : 600; }();
+    a.spin_limit_s = limit;
+  }
   a.q1 = reinterpret_cast<uint8_t*>(d->q1); a.q2 = reinterpret_cast<uint8_t*>(d->q2);
   a.f1 = d->f1; a.f2 = d->f2; a.absmax1 = d->absmax1; a.absmax2 = d->absmax2;
   a.code1 = d->code1; a.code2 = d->code2;

@@ -51,6 +51,7 @@ class B200Group(ctypes.Structure):
         ("beta1", ctypes.c_float), ("beta2", ctypes.c_float), ("eps", ctypes.c_float),
         ("max_grad_norm", ctypes.c_float), ("clamp_value", ctypes.c_float), ("lr", ctypes.c_float),
         ("grad_scale", ctypes.c_float),
+        ("chunk_codec", ctypes.c_void_p),
     ]
 
 

@@ -42,7 +42,12 @@ class FusedGroupAverager:
         self.grad, hg = alloc(n, torch.float32)
         self.param, hp = alloc(n, torch.float32)
         self.shadow, hs = alloc(n, torch.bfloat16)
-        self.payload_mode = {"fp32": 0, "bf16": 1, "u8": 2}[payload]
+        # what a rank exposes to its peers over NVLink.  fp32: the gradient buffer itself; bf16 / u8 (absmax int8 per
+        # 4096 block): a compact copy; fp16 / u8h / adaptive: hivemind's averaging codecs (clamped fp16; uniform 8-bit
+        # with a bucket-mean codebook per 131072-element chunk; `adaptive` = the size rule of reference
+        # task.py:124-126: tensors of 65536 elements and more travel as 8-bit, smaller ones as fp16)
+        self.payload_mode = {"fp32": 0, "bf16": 1, "u8": 2, "fp16": 3, "u8h": 3, "adaptive": 3}[payload]
+        self.payload_name = payload
         # bf16: 2 B / element; u8: 1 B / element + one fp32 step per 4096-element block (fits the same 2 B / element)
         self.payload, hpl = alloc(n if self.payload_mode else 8, torch.bfloat16)
         self.xstride = (2 + 2 * f.n_tensors + 31) // 32 * 32
@@ -63,6 +68,19 @@ class FusedGroupAverager:
             d.payload_ptrs[r], d.xchg_ptrs[r], d.signal_ptrs[r] = hpl.buffer_ptrs[r], hx.buffer_ptrs[r], hsig.buffer_ptrs[r]
         d.xstride, d.n_tensors, d.n_blocks, d.blk0, d.blk1 = self.xstride, f.n_tensors, nb, self.blk0, self.blk1
         d.payload_mode = self.payload_mode
+        self.chunk_codec = None
+        if self.payload_mode == 3:
+            import numpy as np
+
+            from ..optim.lamb8bit import _BLOCK_DTYPE
+
+            quant = f.blocks.cpu().numpy().view(_BLOCK_DTYPE)["quantized"] != 0
+            n_chunks = (nb + 31) // 32
+            big = np.array([quant[32 * c: 32 * c + 32].all() for c in range(n_chunks)])
+            codec = {"fp16": np.full(n_chunks, 3), "u8h": np.full(n_chunks, 4),
+                     "adaptive": np.where(big, 4, 3)}[payload].astype(np.uint8)
+            self.chunk_codec = torch.from_numpy(codec).to(dev)
+            d.chunk_codec = self.chunk_codec.data_ptr()
         d.q1, d.q2, d.f1, d.f2 = f.q1.data_ptr(), f.q2.data_ptr(), f.f1.data_ptr(), f.f2.data_ptr()
         d.absmax1, d.absmax2 = f.absmax1.data_ptr(), f.absmax2.data_ptr()
         d.code1, d.code2 = opt.name2qmap["dynamic"].data_ptr(), opt.name2qmap["udynamic"].data_ptr()

@@ -142,13 +142,16 @@ typedef struct B200Group {
   void* signal_ptrs[8]; void* xchg_ptrs[8];
   int xstride, n_tensors, n_blocks, blk0, blk1;
   unsigned int epoch;
-  int payload_mode;   /* 0: fp32 gradients read over NVLink; 1: bf16 payload (half the bytes) */
+  int payload_mode;   /* 0: fp32 gradients read over NVLink; 1: bf16 payload (half the bytes); 2: absmax int8 per
+                         4096-element block; 3: hivemind's codecs per chunk of 32 blocks (chunk_codec[]: 3 = fp16,
+                         4 = uniform 8-bit with a 256-entry bucket-mean codebook - reference task.py:124-126) */
   int zero_grad;
   int reduce_only;    /* 1: only reduce; every rank ends with grad_scale * sum of all ranks' gradients */
   void* q1; void* q2; float* f1; float* f2; float* absmax1; float* absmax2;
   const float* code1; const float* code2; const void* blocks; const float* wd_per_tensor;
   float* tensor_sums; float* stats /* [4] */; float* trust_out;
   float beta1, beta2, eps, max_grad_norm, clamp_value, lr, grad_scale;
+  const void* chunk_codec;   /* uint8 [ceil(n_blocks / 32)] on the device; payload_mode 3 only */
 } B200Group;
 int b200_group_lamb_step(const B200Group* desc, void* stream);
 

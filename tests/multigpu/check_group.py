@@ -22,16 +22,47 @@ def make(dev, seed=0):
     return ps, opt
 
 
+def make_ttt(dev, seed=0):
+    """The real parameter layout of the TTT model: 423 tensors, 125,894,244 elements, tensors straddling shards."""
+    from dalle_b200.config import ttt_config
+    from dalle_b200.models.dalle import DALLE
+    from dalle_b200.trainer import param_groups
+
+    model = DALLE(ttt_config(), seed=seed).to(dev)
+    opt = LAMB8Bit(param_groups(model, 0.045), lr=1e-2, betas=(0.9, 0.96), eps=1e-6, weight_decay=0.045,
+                   max_grad_norm=0.5, clamp_value=10000.0)
+    opt._build_fused()
+    return opt._fused.layout.params, opt
+
+
+def init_single_rank():
+    """world = 1 (a self-peer): lets a one-GPU box execute the fused kernel."""
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", str(29650 + os.getpid() % 200))
+    torch.cuda.set_device(0)
+    dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+    return 0, 0, 1
+
+
+TOL = {"fp32": 1e-3, "bf16": 3e-3, "u8": 2e-2, "fp16": 3e-3, "u8h": 3e-2, "adaptive": 3e-2}
+GN_TOL = {"fp32": 1e-4, "bf16": 1e-2, "u8": 2e-2, "fp16": 1e-2, "u8h": 4e-2, "adaptive": 4e-2}
+
+
 def main():
     payload = sys.argv[1] if len(sys.argv) > 1 else "fp32"
-    rank, local, world = init_distributed_from_env()
+    layout = sys.argv[2] if len(sys.argv) > 2 else "small"
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        rank, local, world = init_distributed_from_env()
+    else:
+        rank, local, world = init_single_rank()
     dev = torch.device("cuda", local)
-    ps_a, opt_a = make(dev)
-    ps_b, opt_b = make(dev)
+    mk = make_ttt if layout == "ttt" else make
+    ps_a, opt_a = mk(dev)
+    ps_b, opt_b = mk(dev)
     group = FusedGroupAverager(opt_a, payload=payload)
-    for step in range(3):
-        g = torch.Generator().manual_seed(1000 * step + rank)
-        grads = [(torch.randn(p.shape, generator=g) * 0.05).to(dev) for p in ps_a]
+    for step in range(3 if layout == "small" else 2):
+        g = torch.Generator(device=dev).manual_seed(1000 * step + rank)
+        grads = [torch.randn(p.shape, generator=g, device=dev) * 0.05 for p in ps_a]
         for p, q, gr in zip(ps_a, ps_b, grads):
             p.grad.copy_(gr)
             q.grad.copy_(gr)
@@ -42,7 +73,7 @@ def main():
         torch.cuda.synchronize()
         assert not group.step_was_skipped()
         La, Lb = opt_a._fused.layout, opt_b._fused.layout
-        tol = {"fp32": 1e-3, "bf16": 3e-3, "u8": 2e-2}[payload]
+        tol = TOL[payload]
         err = (La.flat - Lb.flat).abs().max().item()
         assert err < tol, f"step {step}: fused vs nccl path differ by {err}"
         assert La.flat_grad.abs().max().item() == 0.0
@@ -53,7 +84,7 @@ def main():
         dist.broadcast(ref, src=0)
         assert torch.equal(mine, ref), "ranks diverged"
         gn_a, gn_b = group.grad_norm(), opt_b.grad_norm() / world  # the single-GPU entry reports the unscaled norm
-        assert abs(gn_a - gn_b) / gn_b < {"fp32": 1e-4, "bf16": 1e-2, "u8": 2e-2}[payload], (gn_a, gn_b)
+        assert abs(gn_a - gn_b) / gn_b < GN_TOL[payload], (gn_a, gn_b)
     # non-finite gradient on ONE rank: every rank skips the step
     before = opt_a._fused.layout.flat.clone()
     for p in ps_a:
@@ -65,7 +96,7 @@ def main():
     assert group.step_was_skipped() and torch.equal(before, opt_a._fused.layout.flat)
     dist.barrier()
     if rank == 0:
-        print(f"GROUP_OK world={world} payload={payload}")
+        print(f"GROUP_OK world={world} payload={payload} layout={layout}")
     dist.destroy_process_group()
 
 
