@@ -41,8 +41,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="micro-batch per GPU")
     ap.add_argument("--preset", default="ttt")
     ap.add_argument("--averaging", default="auto", choices=["auto", "fused", "nccl"])
-    ap.add_argument("--payload", default="fp32", choices=["fp32", "bf16", "u8"],
-                    help="gradient payload of the fused intra-box averaging kernel (u8 = uniform 8-bit, config 3)")
+    ap.add_argument("--payload", default="fp32", choices=["fp32", "bf16", "u8", "fp16", "u8h", "adaptive"],
+                    help="gradient payload of the fused intra-box averaging kernel; adaptive = hivemind's size-adaptive "
+                         "fp16 / uniform-8-bit codecs (BASELINE config 3)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -203,25 +204,25 @@ def main():
     n0 = lib.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
+    # exposed averaging + optimizer time = the part of a step between the end of backward and the next forward,
+    # bracketed by events INSIDE the timed loop (so it stays "exposed" time if the update is ever overlapped)
+    marks = []
     for i in range(K):
-        loss = trainer.step(dev_text[i % n_batches], dev_img[i % n_batches])
-    ev1.record()
-    sync_all()
-    launches = lib.launch_count - n0
-    # exposed averaging + optimizer time (the part of a step that is not forward/backward), device-timed
-    exposed_ms = None
-    if args.impl == "b200":
-        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        tot = 0.0
-        for i in range(3):
-            trainer.accumulate(dev_text[i % n_batches], dev_img[i % n_batches])
-            sync_all()
+        if args.impl == "b200":
+            loss = trainer.accumulate(dev_text[i % n_batches], dev_img[i % n_batches])
+            ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ea.record()
             trainer.optimizer_step()
             eb.record()
-            torch.cuda.synchronize()
-            tot += ea.elapsed_time(eb)
-        t = torch.tensor([tot / 3], device=dev)
+            marks.append((ea, eb))
+        else:
+            loss = trainer.step(dev_text[i % n_batches], dev_img[i % n_batches])
+    ev1.record()
+    sync_all()
+    launches = lib.launch_count - n0
+    exposed_ms = None
+    if marks:
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in marks) / len(marks)], device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         exposed_ms = t.item()

@@ -178,8 +178,11 @@ group_lamb_kernel(const GroupArgs a) {
           uint32_t o[EPT / 2];
 #pragma unroll
           for (int j = 0; j < EPT; j += 2) {
-            const __half2 hv = __floats2half2_rn(fminf(fmaxf(s16[j], -65504.f), 65504.f),
-                                                 fminf(fmaxf(s16[j + 1], -65504.f), 65504.f));
+            // finite values are clamped into the fp16 range (hivemind's Float16Compression); Inf / NaN stay what
+            // they are so that the reducer's finite flag still sees them
+            const float x0 = s16[j], x1 = s16[j + 1];
+            const __half2 hv = __floats2half2_rn(isfinite(x0) ? fminf(fmaxf(x0, -65504.f), 65504.f) : x0,
+                                                 isfinite(x1) ? fminf(fmaxf(x1, -65504.f), 65504.f) : x1);
             o[j / 2] = *reinterpret_cast<const uint32_t*>(&hv);
           }
           uint4* d4 = reinterpret_cast<uint4*>(dst + (static_cast<long long>(b - b0) * QBLOCK + e0) * 2);
