@@ -164,7 +164,9 @@ group_lamb_kernel(const GroupArgs a) {
   }
   if (a.payload_mode == 3) {
     // my gradients -> hivemind payload, one CTA per chunk
-    __shared__ float h_sum[256];
+    // bucket sums as 64-bit fixed point of the in-bin residual: shared-memory float atomics are compare-and-swap loops
+    // (the first version of this encoder cost 7 ms per step), integer ones are native
+    __shared__ unsigned long long h_res[256];
     __shared__ int h_cnt[256];
     const int n_chunks = (a.n_blocks + CHUNK_BLOCKS - 1) / CHUNK_BLOCKS;
     uint8_t* pay = reinterpret_cast<uint8_t*>(a.payload[a.rank]);
@@ -210,7 +212,7 @@ group_lamb_kernel(const GroupArgs a) {
       const bool finite = isfinite(scale) && isfinite(mu);
       if (!(scale > 0.f)) scale = 1.0f;
       const float inv = 1.0f / scale;
-      h_sum[threadIdx.x] = 0.f;
+      h_res[threadIdx.x] = 0ull;
       h_cnt[threadIdx.x] = 0;
       __syncthreads();
       for (int b = b0; b < b1; ++b) {
@@ -222,8 +224,10 @@ group_lamb_kernel(const GroupArgs a) {
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const float x = s16[j + e];
-            const int q = min(max(__float2int_rn((x - mu) * inv) + 128, 0), 255);   // round half to even
-            atomicAdd(&h_sum[q], x);
+            const float t = (x - mu) * inv;
+            const int q = min(max(__float2int_rn(t) + 128, 0), 255);   // round half to even
+            const float r = fminf(fmaxf(t - static_cast<float>(q - 128), -1e6f), 1e6f);   // residual in bin widths
+            atomicAdd(&h_res[q], static_cast<unsigned long long>(__float2ll_rn(r * 1048576.f)));
             atomicAdd(&h_cnt[q], 1);
             w |= static_cast<uint32_t>(q) << (8 * e);
           }
@@ -234,7 +238,13 @@ group_lamb_kernel(const GroupArgs a) {
       __syncthreads();
       // codebook = bucket means of the ORIGINAL values; a non-finite chunk stays visible as NaN to the reducer
       float* book = reinterpret_cast<float*>(dst + static_cast<long long>(b1 - b0) * QBLOCK);   // right behind the codes
-      book[threadIdx.x] = finite ? h_sum[threadIdx.x] / static_cast<float>(max(h_cnt[threadIdx.x], 1)) : NAN;
+      {
+        const int cnt = h_cnt[threadIdx.x];
+        const float mean_r = cnt > 0 ? static_cast<float>(static_cast<double>(static_cast<long long>(h_res[threadIdx.x])) *
+                                                          (1.0 / 1048576.0) / cnt) : 0.f;
+        const float val = cnt > 0 ? mu + (static_cast<float>(static_cast<int>(threadIdx.x) - 128) + mean_r) * scale : 0.f;
+        book[threadIdx.x] = finite ? val : NAN;
+      }
       __syncthreads();
     }
   }
