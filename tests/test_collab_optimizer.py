@@ -85,3 +85,76 @@ def test_single_peer_uses_local_gradients_and_late_joiner_loads_state():
 def test_compression_choice_matches_reference_threshold():
     c = SizeAdaptiveCompression(threshold=2 ** 16 + 1, less=Float16Compression(), greater_equal=Uniform8BitQuantization())
     assert c.choose(65536).name == "fp16" and c.choose(65537).name == "u8"
+
+
+def test_grad_scaler_defers_unscale_and_update_to_global_steps():
+    """HivemindGradScaler (reference hf_trainer.py:26-28): gradients accumulated over micro-steps keep ONE
+    loss scale - unscale_ / update are no-ops between global steps and run once inside the global step."""
+    from dalle_b200.collab.optimizer import HivemindGradScaler
+
+    d0 = _dht()
+    try:
+        model, opt = _make(d0, "scaler", bs=8, target=16, lr=0.5)
+        scaler = HivemindGradScaler(device="cpu", init_scale=1024.0, growth_interval=1, enabled=True)
+        w0 = model.weight.detach().clone()
+        x = torch.ones(4, 8)
+        for micro in range(2):            # two micro-steps = one global step (target 16, 8 per step)
+            loss = model(x).sum()
+            scaler.scale(loss).backward()
+            assert scaler.unscale_(opt) is False      # deferred: the accumulated gradients stay scaled by 1024
+            if micro == 0:
+                assert abs(model.weight.grad.mean().item() - 4.0 * 1024.0) < 1e-3
+            scaler.step(opt)
+            scaler.update()
+            if micro == 0:
+                assert scaler.get_scale() == 1024.0 and opt.local_epoch == 0
+        assert opt.local_epoch == 1
+        # the wrapped SGD saw the UNSCALED mean gradient of the two micro-steps: d(sum)/dw = 4 per element
+        assert torch.allclose(w0 - model.weight.detach(), torch.full_like(w0, 0.5 * 4.0), atol=1e-4)
+        assert scaler.get_scale() == 2048.0           # one update, at the global step
+        opt.shutdown()
+    finally:
+        d0.shutdown()
+
+
+def test_nan_in_parameters_rolls_back_to_the_local_backup(tmp_path):
+    """callback.on_step_end: a non-finite parameter restores model + optimizer + scheduler + epoch from state_path
+    (reference callback.py:50-55, 115-127); without a backup it raises."""
+    import types
+
+    import pytest
+
+    import callback as cbmod
+
+    d0 = _dht()
+    try:
+        model, opt = _make(d0, "nanroll", bs=16, target=16, lr=0.1)
+        task = types.SimpleNamespace(dht=d0, collaborative_optimizer=opt, model=model, local_public_key=b"k")
+        args = types.SimpleNamespace(statistics_expiration=60, backup_every_steps=1, state_path=str(tmp_path / "s.zip"))
+        cb = cbmod.CollaborativeCallback(task, args)
+
+        def micro_step():
+            for p in model.parameters():
+                p.grad = torch.ones_like(p) if p.grad is None else p.grad.add_(1.0)
+            opt.step()
+            cb.on_step_end(loss=1.0)
+
+        with torch.no_grad():
+            model.weight[0, 0] = float("nan")
+        with pytest.raises(RuntimeError, match="no backup"):
+            cb.on_step_end(loss=1.0)
+        with torch.no_grad():
+            model.weight[0, 0] = 0.0
+        micro_step()                                   # epoch 1 -> backup written
+        assert (tmp_path / "s.zip").exists() and opt.local_epoch == 1
+        good = model.weight.detach().clone()
+        micro_step()                                   # epoch 2 (backup refreshed)
+        good2, epoch2 = model.weight.detach().clone(), opt.local_epoch
+        with torch.no_grad():
+            model.weight[0, 3] = float("inf")
+        cb.on_step_end(loss=1.0)                       # guard fires, state comes back from the file
+        assert torch.isfinite(model.weight).all() and torch.equal(model.weight.detach(), good2)
+        assert opt.local_epoch == epoch2 and not torch.equal(good, good2)
+        opt.shutdown()
+    finally:
+        d0.shutdown()

@@ -91,3 +91,34 @@ def test_gpu_cross_entropy_segment():
         res[dev] = (loss.cpu(), lg[:, :n].float().cpu())
     assert abs(res["cpu"][0].item() - res["cuda"][0].item()) < 1e-3
     assert (res["cpu"][1] - res["cuda"][1]).abs().max().item() < 2e-4
+
+
+def test_ttt_dimension_stack_matches_fp32_oracle():
+    """Depth-2 stack at the TTT dimensions (dim 1024, 16 heads, 257 + 1024 tokens, vocab 40548), batch 1, against the
+    fp32 oracle: loss and EVERY gradient, by maximum error and by per-tensor cosine."""
+    from dalle_b200.config import ttt_config
+
+    cfg = ttt_config(depth=2, attn_types=("axial_row", "axial_col"), shared_attn_ids=(0, 1), shared_ff_ids=(0, 1))
+    ref = DALLE(cfg, seed=0)
+    _boost(ref)
+    model = DALLE(cfg, seed=0)
+    model.load_state_dict(ref.state_dict())
+    model.cuda()
+    text, image = _batch(cfg, b=1)
+    ref.cuda()   # the oracle runs in fp32 on the GPU (cuBLAS / ATen): 40548-wide logits on the CPU would take minutes
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref_loss = ref.forward_reference(text.cuda(), image.cuda(), return_loss=True)
+    ref_grads = torch.autograd.grad(ref_loss, list(ref.parameters()))
+    loss = model(text.cuda(), image.cuda(), return_loss=True)
+    assert abs(loss.item() - ref_loss.item()) < 3e-2, (loss.item(), ref_loss.item())
+    loss.backward()
+    torch.cuda.synchronize()
+    bad = []
+    for (name, p), g in zip(model.named_parameters(), ref_grads):
+        assert p.grad is not None and torch.isfinite(p.grad).all(), name
+        err = (p.grad - g).abs().max().item()
+        den = g.abs().max().item() + 1e-12
+        cos = torch.nn.functional.cosine_similarity(p.grad.flatten().double(), g.flatten().double(), dim=0).item()
+        if err / den > 6e-2 or cos < 0.999:
+            bad.append((name, round(err / den, 4), round(cos, 5)))
+    assert not bad, bad
