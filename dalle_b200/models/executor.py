@@ -51,6 +51,13 @@ class Engine:
         self.cfg = model.cfg
         env = os.environ.get("DALLE_B200_STORE_LAYERS")
         self.store_layers = int(env) if env not in (None, "") else store_layers   # None: as many as fit
+        # Training loops that ALWAYS call backward after a training forward, with a gradient they know beforehand
+        # (1 for `loss.backward()`, 1 / accum for `(loss / accum).backward()`), set this to that value: the forward's
+        # single pass over the logits then also produces the loss gradient (d logits -> d hidden, tied-matrix
+        # gradients) and the backward does not touch the head again - one logits GEMM and one cross-entropy pass fewer
+        # per step.  None (default) keeps the two-pass form, which is right for any use (forward without backward,
+        # unknown upstream gradient).
+        self.expected_grad_out: Optional[float] = None
         self._bufs: Dict[tuple, _Buffers] = {}
         self._shadow: Dict[int, torch.Tensor] = {}
         self._shadow_version: Dict[int, int] = {}
@@ -280,7 +287,7 @@ class Engine:
                 (nt, ni, cfg.total_text_tokens, cfg.num_image_tokens, b.ld_i, b.chunk_i, wi))
 
     def _head(self, B, b, labels_t, labels_i, grad_scale: Optional[torch.Tensor]):
-        """Loss (grad_scale None) or loss-gradient pass (writes b.dhf and accumulates the tied-matrix grads)."""
+        """Loss (grad_scale None) or loss + loss-gradient pass (writes b.dhf and accumulates the tied-matrix grads)."""
         m, cfg = self.model, self.cfg
         W = self.w(m.emb_weight)
         bias = m.emb_bias.detach()
@@ -393,15 +400,25 @@ class Engine:
         self.run_stack(ids, b)
         self.final_norm(b)
         b.loss.zero_()
-        self._head(B, b, labels_t.view(-1), image.reshape(-1), None)
+        b.head_grad_done = False
+        gs = None
+        if train and self.expected_grad_out is not None:
+            gs = torch.full((1,), float(self.expected_grad_out), device=dev, dtype=torch.float32)
+            b.head_grad_done = True
+        self._head(B, b, labels_t.view(-1), image.reshape(-1), gs)
         return b.loss[0].clone(), ids, labels_t
 
     def _backward(self, B, b, ids, labels_t, image, grad_out: torch.Tensor):
         m, cfg = self.model, self.cfg
-        scratch_loss = b.loss.clone()
-        gs = grad_out.detach().reshape(1).to(torch.float32)
-        self._head(B, b, labels_t.view(-1), image.reshape(-1), gs)
-        b.loss.copy_(scratch_loss)
+        if not getattr(b, "head_grad_done", False):
+            scratch_loss = b.loss.clone()
+            gs = grad_out.detach().reshape(1).to(torch.float32)
+            self._head(B, b, labels_t.view(-1), image.reshape(-1), gs)
+            b.loss.copy_(scratch_loss)
+        elif os.environ.get("DALLE_B200_CHECK_GRAD_OUT"):   # debugging aid: verifies the promise (host sync)
+            assert abs(float(grad_out) - float(self.expected_grad_out)) < 1e-6 * max(1.0, abs(float(grad_out))), \
+                f"backward got grad_out {float(grad_out)} but expected_grad_out is {self.expected_grad_out}"
+        b.head_grad_done = False
         E.ln_shift_bwd(b.dhf, b.x1, b.x2, b.fmean, b.frstd, m.final_norm_w, b.dx1, b.dx2,
                        self.grad_of(m.final_norm_w), self.grad_of(m.final_norm_b), cfg, False, 1,
                        row_split=cfg.text_seq_len)

@@ -63,6 +63,10 @@ class GroupTrainer:
             self.payload = payload
             self.group = FusedGroupAverager(self.opt, process_group, payload=payload)
         self.steps = 0
+        # step() / accumulate() always run backward on the unscaled loss: the head's gradient is formed in the forward
+        # pass (models/executor.py: expected_grad_out)
+        if self.device.type == "cuda":
+            self.model.engine.expected_grad_out = 1.0
         from .utils.phases import PhaseTrace
 
         self.trace = PhaseTrace()   # NVTX ranges + device-timed phases when DALLE_B200_TRACE=1

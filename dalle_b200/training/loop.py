@@ -89,6 +89,9 @@ class CollaborativeTrainer:
             cb.on_train_begin()
         accum = max(1, self.args.gradient_accumulation_steps)
         micro, t_log, loss_log = 0, time.time(), 0.0
+        inner = getattr(self.model, "model", self.model)
+        if self.device.type == "cuda" and hasattr(inner, "engine"):
+            inner.engine.expected_grad_out = 1.0 / accum   # this loop always calls (loss / accum).backward()
         for batch in self.get_train_dataloader():
             batch = {k: v.to(self.device, non_blocking=True) for k, v in batch.items()}
             loss = self.model(**batch)["loss"]

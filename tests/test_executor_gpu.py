@@ -122,3 +122,27 @@ def test_ttt_dimension_stack_matches_fp32_oracle():
         if err / den > 6e-2 or cos < 0.999:
             bad.append((name, round(err / den, 4), round(cos, 5)))
     assert not bad, bad
+
+
+def test_head_gradient_in_the_forward_pass_gives_the_same_gradients():
+    """engine.expected_grad_out: the loss gradient of the head is formed during the forward pass (one logits GEMM and
+    one cross-entropy pass fewer) - same loss, same gradients as the two-pass form, also for a scaled backward."""
+    cfg = small_config()
+    text, image = _batch(cfg)
+    grads = {}
+    base = DALLE(cfg, seed=0)
+    _boost(base)
+    for mode, scale in (("two-pass", 0.5), ("fused", 0.5)):
+        model = DALLE(cfg, seed=0)
+        model.load_state_dict(base.state_dict())
+        model.cuda()
+        if mode == "fused":
+            model.engine.expected_grad_out = scale
+        loss = model(text.cuda(), image.cuda(), return_loss=True)
+        (loss * scale).backward()
+        torch.cuda.synchronize()
+        grads[mode] = (loss.item(), {n: p.grad.clone() for n, p in model.named_parameters()})
+    assert abs(grads["two-pass"][0] - grads["fused"][0]) < 1e-5
+    for n, g in grads["two-pass"][1].items():
+        d = (g - grads["fused"][1][n]).abs().max().item()
+        assert d <= 2e-3 * (g.abs().max().item() + 1e-8), (n, d)
