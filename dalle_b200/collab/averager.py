@@ -18,6 +18,8 @@ from __future__ import annotations
 import asyncio
 import contextlib
 import enum
+import hashlib
+import logging
 import os
 import threading
 import time
@@ -30,6 +32,8 @@ import torch
 from ..dht import DHT, get_dht_time
 from ..transport.p2p import P2PError, PeerID, Stream
 from . import compression as C
+
+logger = logging.getLogger(__name__)
 
 
 def _bulk_available() -> bool:
@@ -207,6 +211,11 @@ class DecentralizedAverager:
             if isinstance(src, torch.Tensor):
                 dst.copy_(src.detach().cpu())
         self._partition = Partition(self._sizes, compression, self.part_elems)
+        # what two peers must agree on to average the same thing: tensor sizes in order and the part boundaries
+        # (which follow from the sizes, the codec choice per tensor and the part size).  Declared with the
+        # matchmaking record and checked in the join handshake; a peer with another schema is never grouped.
+        self.schema = hashlib.sha1(repr((self._sizes, [(a, b) for a, b, _ in self._partition.parts])).encode()).hexdigest()[:16]
+        self._schema_warned: set = set()
         self.lock_averaged_tensors = threading.Lock()
         self._rounds: Dict[bytes, _Round] = {}
         self._round_waiters: Dict[bytes, asyncio.Future] = {}
@@ -280,7 +289,14 @@ class DecentralizedAverager:
     def _my_info(self, gather, deadline):
         ep = self.dht.p2p.endpoint
         return {"pid": self.dht.peer_id.raw, "ep": list(ep) if ep else None, "mode": int(self.mode),
-                "deadline": deadline, "gather": gather, "bw": self.bandwidth}
+                "deadline": deadline, "gather": gather, "bw": self.bandwidth, "schema": self.schema}
+
+    def _warn_schema(self, who: bytes, theirs):
+        if who not in self._schema_warned:
+            self._schema_warned.add(who)
+            logger.warning(f"{self.prefix}: peer {who.hex()[:12] if not who.startswith(b'leader@') else who.decode()} "
+                           f"declares tensor schema {theirs}, this peer has {self.schema} (different model, codec or "
+                           f"part size) - not grouping with it")
 
     async def _declared(self):
         entry = await self.dht.node.get(f"{self.prefix}.matchmaking", latest=True)
@@ -290,6 +306,9 @@ class DecentralizedAverager:
             for pid, v in entry.value.items():
                 d = v.value
                 if d and d.get("ep") and v.expiration_time > now:
+                    if d.get("schema", self.schema) != self.schema:
+                        self._warn_schema(bytes(pid), d.get("schema"))
+                        continue
                     out.append((d["deadline"], bytes(pid), tuple(d["ep"])))
         return sorted(out)
 
@@ -302,7 +321,8 @@ class DecentralizedAverager:
         self._assembled = asyncio.get_event_loop().create_future()
         try:
             if self.mode != AveragingMode.CLIENT:
-                await self.dht.node.store(f"{self.prefix}.matchmaking", {"ep": info["ep"], "deadline": deadline},
+                await self.dht.node.store(f"{self.prefix}.matchmaking",
+                                          {"ep": info["ep"], "deadline": deadline, "schema": self.schema},
                                           deadline + 1.0, subkey=me)
             tried_at: Dict[bytes, float] = {}
             while True:
@@ -355,6 +375,10 @@ class DecentralizedAverager:
                 await stream.send({"status": "rejected"})
                 return
             pid = bytes(payload["pid"])
+            if payload.get("schema") != self.schema:
+                self._warn_schema(pid, payload.get("schema"))
+                await stream.send({"status": "schema_mismatch", "schema": self.schema})
+                return
             self._followers[pid] = {"info": payload}
             await stream.send({"status": "accepted"})
             assembled = self._assembled
@@ -379,6 +403,8 @@ class DecentralizedAverager:
             return None
         try:
             msg = await stream.recv(self.request_timeout)
+            if msg.get("status") == "schema_mismatch":
+                self._warn_schema(b"leader@" + repr(tuple(leader_ep)).encode(), msg.get("schema"))
             if msg.get("status") != "accepted":
                 return None
             msg = await stream.recv(wait + self.request_timeout)

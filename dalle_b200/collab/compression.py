@@ -6,8 +6,9 @@
   wire = int64(256) | L (256 x fp32) | q (n x uint8); decode x^_i = L[q_i].
 * ``SizeAdaptiveCompression(threshold, less, greater_equal)``: chosen by the whole tensor's numel.
 
-The PyTorch code below is the oracle; CPU tensors use the C++ host implementation (native/compress_host.cpp) when
-built, CUDA tensors the device kernels (csrc/compress.cu).
+The PyTorch code below is the oracle and the wire-format owner; CPU tensors go through the C++ host codec
+(native/quant_host.cpp, ``dalle_b200.native.host``) when it is built.  On the GPU the same two codecs run inside the
+fused averaging kernel (ops/csrc/group_avg.cu, payload mode 3) and never produce a separate serialized tensor.
 """
 from __future__ import annotations
 

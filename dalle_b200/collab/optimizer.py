@@ -308,7 +308,6 @@ class Optimizer:
         self._apply_finished_state_round()
         if grad_scaler is not None and not grad_scaler.are_grads_finite(self):
             logger.info("encountered non-finite gradients, skipping this micro-step")
-            self.grad_averager.reset_accumulated_grads_() if False else None
             return loss
         if not self.is_synchronized_with_peers():
             logger.info(f"peer is out of sync (local epoch {self.local_epoch}, global {self.tracker.global_epoch}): "

@@ -1,7 +1,10 @@
 """Sparse DALL-E attention core: (rotated, pre-scaled) qkv -> o, with its backward.
 
-GPU tensors run the tcgen05 kernels (csrc/attn_fwd_sm100.cu, attn_bwd_sm100.cu); CPU tensors run the dense-mask
-PyTorch statement below, which is also the oracle of the GPU tests.
+GPU tensors run the tcgen05 kernels: axial row / column layers go to csrc/attn_fwd4_sm100.cu and
+attn_bwd4_sm100.cu (64-key chunks, P and dS consumed from TMEM), the convolution-like layer to attn_fwd2_sm100.cu and
+attn_bwd_sm100.cu, and image grids wider than 32 to the first-generation forward in attn_fwd_sm100.cu
+(``DALLE_B200_ATTN_FWD`` / ``DALLE_B200_ATTN_BWD`` select an older generation for A/B runs).  CPU tensors run the
+dense-mask PyTorch statement below, which is also the oracle of the GPU tests.
 """
 from __future__ import annotations
 

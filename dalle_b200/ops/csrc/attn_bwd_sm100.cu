@@ -487,7 +487,7 @@ extern "C" int b200_attn_bwd(const void* qkv, const void* out, const void* d_out
   AttnGeom g;
   g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
   g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = conv_kernel / 2;
-  if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
+  if (g.P % 128 || 32 % F || seq != T + g.P - 1) return -30;   // grid sides 16 and 32, as in the forward
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // text + axial patterns: the fourth-generation kernels (attn_bwd4_sm100.cu); DALLE_B200_ATTN_BWD=2 keeps this file's
   // kernel for A/B runs

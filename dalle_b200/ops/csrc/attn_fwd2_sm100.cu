@@ -201,12 +201,33 @@ static int launch_fwd2(const CUtensorMap& t128, const CUtensorMap& ttail, const 
   return cudaGetLastError() == cudaSuccess ? 0 : -22;
 }
 
+int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
+                   CUtensorMap* taux) {
+  const uint64_t rows = (uint64_t)g.B * g.seq, cols = 3ull * g.H * 64;
+  int rc = make_tmap_bf16_2d(t128, qkv, rows, cols, cols, 64, 128);
+  if (rc) return rc;
+  const int tail = g.T_pad % 128;
+  rc = make_tmap_bf16_2d(ttail, qkv, rows, cols, cols, 64, tail ? tail : 128);
+  if (rc) return rc;
+  if (mode == ATT_COL) {
+    // image part viewed as [b][r][c][feature]; one box = one image column (F tokens, stride F rows)
+    const __nv_bfloat16* base = reinterpret_cast<const __nv_bfloat16*>(qkv) + (size_t)g.T * cols;
+    // the last image position has no token: rows r = F-1 expose F-1 columns only for the last sample -> the
+    // tensor map is declared over the full grid; reads past the allocation are avoided by bounding dim 3 (batch)
+    // and letting the final element fall into the next sample / OOB fill.
+    uint64_t dims[4] = {cols, (uint64_t)g.F, (uint64_t)g.F, (uint64_t)g.B};
+    uint64_t strides[3] = {cols * 2, cols * 2 * g.F, cols * 2 * g.seq};
+    uint32_t box[4] = {64, 1, (uint32_t)g.F, 1};
+    rc = make_tmap_bf16_nd(taux, base, 4, dims, strides, box);
+  } else {
+    rc = make_tmap_bf16_2d(taux, qkv, rows, cols, cols, 64, 2 * g.F);
+  }
+  return rc;
+}
+
 }  // namespace b200
 
 using namespace b200;
-
-extern "C" int b200_attn_fwd_v1(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
-                                int conv_kernel, void* stream);
 
 extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode,
                              int conv_kernel, void* stream) {
@@ -214,9 +235,12 @@ extern "C" int b200_attn_fwd(const void* qkv, void* out, float* lse, int B, int 
   g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
   g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = conv_kernel / 2;
   if (g.P % 128 || 128 % F || seq != T + g.P - 1) return -30;
-  // the softmax warps assume that a query's local keys sit inside its own 32-key window (grid side 16 or 32);
-  // wider grids take the first-generation kernel, which keeps whole score rows in TMEM
-  if (32 % F) return b200_attn_fwd_v1(qkv, out, lse, B, H, seq, T, F, mode, conv_kernel, stream);
+  // the softmax warps assume that a query's local keys sit inside its own 32-key window: grid sides 16 and 32
+  // (the reference fixes 32, task.py:26).  Wider grids are refused here and in the backward, not approximated.
+  if (32 % F) {
+    fprintf(stderr, "b200_attn_fwd: image grid side %d is not supported by the sm_100a kernels (16 or 32)\n", F);
+    return -30;
+  }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // text + axial patterns have three forward kernels; DALLE_B200_ATTN_FWD = 2 | 3 | 4 picks one for A/B runs:
   //   4  (default) many light CTAs, 64-key chunks, P and O in TMEM (attn_fwd4_sm100.cu)

@@ -6,11 +6,12 @@
 // (TN, both operands MN-major, split-K with fp32 red.add into the shared .grad buffer - weight sharing
 // means 16 layers accumulate into one gradient, reference task.py:65-66).
 //
-// Persistent kernel: grid = min(#work units, #SMs); each CTA has 6 warps:
+// Persistent kernel: grid = min(#work units, #SMs); each CTA has 10 warps:
 //   warp 0  : TMA producer            (one lane)
 //   warp 1  : TMEM allocator + MMA issuer (one lane)
 //   warps 2-9: epilogue, warp w owns TMEM lanes 32*(w%4)..+31 (one output row per thread) and one half of the
 //              256 accumulator columns
+#include <cstring>
 #include "sm100_cg2.cuh"
 #include "b200_api.h"
 #include <cstdlib>
@@ -830,51 +831,43 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// Row-major bf16 matrix [rows, cols] with leading dimension ld (elements); box {box_cols, box_rows}.
-int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
-                      uint32_t box_cols, uint32_t box_rows) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return -1;
-  cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {ld * 2};
-  cuuint32_t box[2] = {box_cols, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : -2;
+// A CUtensorMap is a pure function of the encode arguments (it holds the address and the geometry, the driver keeps
+// nothing behind it), and a training step asks for the same few hundred maps every step: keep the encoded maps in
+// a per-thread direct-mapped table keyed on every argument, so that a steady-state launch costs a hash and a
+// compare instead of a driver call per operand.
+struct TmapKey {
+  const void* ptr;
+  uint64_t dim[5];
+  uint64_t str[4];
+  uint32_t box[5];
+  int32_t dtype, rank, swizzle;
+};
+struct TmapSlot {
+  TmapKey key;
+  CUtensorMap map;
+  bool used;
+};
+constexpr int kTmapSlots = 2048;
+
+static uint64_t tmap_hash(const TmapKey& k) {
+  const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+  uint64_t h = 0x9E3779B97F4A7C15ull;
+  for (size_t i = 0; i < sizeof(TmapKey) / 8; ++i) { h ^= w[i]; h *= 0xFF51AFD7ED558CCDull; h ^= h >> 29; }
+  return h;
 }
 
-// Output-side map for the staged epilogue: box {32 columns, 32 rows}, 64-byte swizzle.
-int make_tmap_bf16_out(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return -1;
-  cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {ld * 2};
-  cuuint32_t box[2] = {32, 32};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : -2;
-}
-
-// fp32 tile map of the residual epilogue: box {32 columns, 32 rows} = 128-byte rows, 128-byte swizzle.
-int make_tmap_f32_tile(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (!fn) return -1;
-  cuuint64_t gdim[2] = {cols, rows};
-  cuuint64_t gstr[1] = {ld * 4};
-  cuuint32_t box[2] = {32, 32};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : -2;
-}
-
-int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                      const uint32_t* box) {
+static int encode_cached(CUtensorMap* m, CUtensorMapDataType dtype, int rank, const void* ptr, const uint64_t* dims,
+                         const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swizzle) {
+  static_assert(sizeof(TmapKey) % 8 == 0, "hashed by 8-byte words");
+  static thread_local TmapSlot* table = nullptr;
+  if (table == nullptr) table = new TmapSlot[kTmapSlots]();
+  TmapKey k;
+  memset(&k, 0, sizeof(k));
+  k.ptr = ptr; k.dtype = static_cast<int32_t>(dtype); k.rank = rank; k.swizzle = static_cast<int32_t>(swizzle);
+  for (int i = 0; i < rank; ++i) { k.dim[i] = dims[i]; k.box[i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) k.str[i] = strides_bytes[i];
+  TmapSlot& slot = table[tmap_hash(k) & (kTmapSlots - 1)];
+  if (slot.used && memcmp(&slot.key, &k, sizeof(k)) == 0) { *m = slot.map; return 0; }
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return -1;
   cuuint64_t gdim[5];
@@ -883,10 +876,40 @@ int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t*
   cuuint32_t estr[5];
   for (int i = 0; i < rank; ++i) { gdim[i] = dims[i]; bx[i] = box[i]; estr[i] = 1; }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), gdim, gstr, bx, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : -2;
+  CUresult r = fn(m, dtype, rank, const_cast<void*>(ptr), gdim, gstr, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return -2;
+  slot.key = k; slot.map = *m; slot.used = true;
+  return 0;
+}
+
+// Row-major bf16 matrix [rows, cols] with leading dimension ld (elements); box {box_cols, box_rows}.
+int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_cols, uint32_t box_rows) {
+  const uint64_t gdim[2] = {cols, rows}, gstr[1] = {ld * 2};
+  const uint32_t box[2] = {box_cols, box_rows};
+  return encode_cached(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, gdim, gstr, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+// Output-side map for the staged epilogue: box {32 columns, 32 rows}, 64-byte swizzle.
+int make_tmap_bf16_out(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
+  const uint64_t gdim[2] = {cols, rows}, gstr[1] = {ld * 2};
+  const uint32_t box[2] = {32, 32};
+  return encode_cached(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, ptr, gdim, gstr, box, CU_TENSOR_MAP_SWIZZLE_64B);
+}
+
+// fp32 tile map of the residual epilogue: box {32 columns, 32 rows} = 128-byte rows, 128-byte swizzle.
+int make_tmap_f32_tile(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld) {
+  const uint64_t gdim[2] = {cols, rows}, gstr[1] = {ld * 4};
+  const uint32_t box[2] = {32, 32};
+  return encode_cached(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, gdim, gstr, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box) {
+  if (rank < 1 || rank > 5) return -2;
+  return encode_cached(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, ptr, dims, strides_bytes, box,
+                       CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 int num_sms() {

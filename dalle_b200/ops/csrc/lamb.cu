@@ -176,6 +176,9 @@ lamb_apply_kernel(float* __restrict__ g, float* __restrict__ p, __nv_bfloat16* _
 
 using namespace b200;
 
+namespace b200 { int num_sms(); }  // gemm_sm100.cu
+static int grad_norm_grid() { return b200::num_sms() * 8; }   // eight 256-thread blocks per SM, grid-stride
+
 extern "C" int b200_lamb_step(float* grad, float* param, void* param_bf16, long long n_padded, void* q1, void* q2,
                               float* f1, float* f2, float* absmax1, float* absmax2, const float* code1,
                               const float* code2, const void* blocks, int n_blocks, const float* wd_per_tensor,
@@ -189,7 +192,7 @@ extern "C" int b200_lamb_step(float* grad, float* param, void* param_bf16, long 
   hp.lr = lr; hp.grad_scale = grad_scale; hp.use_clip = max_grad_norm > 0.f;
   cudaMemsetAsync(stats, 0, 2 * sizeof(float), st);
   cudaMemsetAsync(tensor_sums, 0, 2 * n_tensors * sizeof(float), st);
-  lamb_grad_norm_kernel<<<148 * 8, LAMB_THREADS, 0, st>>>(grad, n_padded, stats);
+  lamb_grad_norm_kernel<<<grad_norm_grid(), LAMB_THREADS, 0, st>>>(grad, n_padded, stats);
   lamb_moments_kernel<<<n_blocks, LAMB_THREADS, 0, st>>>(
       grad, param, reinterpret_cast<uint8_t*>(q1), reinterpret_cast<uint8_t*>(q2), f1, f2, absmax1, absmax2, code1,
       code2, reinterpret_cast<const LambBlock*>(blocks), wd_per_tensor, tensor_sums, stats, hp);
@@ -278,16 +281,20 @@ extern "C" int b200_lamb_step_noalloc(float* grad, float* param, void* param_bf1
   hp.beta1 = beta1; hp.beta2 = beta2; hp.eps = eps; hp.max_grad_norm = max_grad_norm; hp.clamp_value = clamp_value;
   hp.lr = lr; hp.grad_scale = grad_scale; hp.use_clip = max_grad_norm > 0.f;
   // the previous call's statistics and partial sums are still in the array: clear what accumulates
-  cudaMemsetAsync(stats, 0, 2 * sizeof(float), st);
-  cudaMemsetAsync(tensor_sums, 0, 2 * static_cast<size_t>(n_tensors) * sizeof(float), st);
-  lamb_grad_norm_kernel<<<148 * 8, LAMB_THREADS, 0, st>>>(grad, n_padded, stats);
+  if (cudaMemsetAsync(stats, 0, 2 * sizeof(float), st) != cudaSuccess) return B200_ERR_NOALLOC_SETUP;
+  if (n_tensors > 0 &&
+      cudaMemsetAsync(tensor_sums, 0, 2 * static_cast<size_t>(n_tensors) * sizeof(float), st) != cudaSuccess)
+    return B200_ERR_NOALLOC_SETUP;
+  lamb_grad_norm_kernel<<<grad_norm_grid(), LAMB_THREADS, 0, st>>>(grad, n_padded, stats);
   lamb_moments_kernel<<<n_blocks, LAMB_THREADS, 0, st>>>(
       grad, param, reinterpret_cast<uint8_t*>(q1), reinterpret_cast<uint8_t*>(q2), f1, f2, absmax1, absmax2, code1,
       code2, reinterpret_cast<const LambBlock*>(blocks), wd_per_tensor, tensor_sums, stats, hp);
   lamb_apply_kernel<<<n_blocks, LAMB_THREADS, 0, st>>>(grad, param, reinterpret_cast<__nv_bfloat16*>(param_bf16),
                                                        reinterpret_cast<const LambBlock*>(blocks), tensor_sums,
                                                        trust_out, stats, hp, zero_grad);
-  if (stats_out != nullptr)  // {sum g^2, non-finite flag} for callers that want to look at them
-    cudaMemcpyAsync(stats_out, stats, 2 * sizeof(float), cudaMemcpyDeviceToDevice, st);
-  return cudaGetLastError() == cudaSuccess ? 0 : -51;
+  if (cudaGetLastError() != cudaSuccess) return -51;
+  if (stats_out != nullptr &&  // {sum g^2, non-finite flag} for callers that want to look at them
+      cudaMemcpyAsync(stats_out, stats, 2 * sizeof(float), cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+    return -51;
+  return 0;
 }

@@ -91,6 +91,7 @@ class GroupTrainer:
         if self.world > 1:
             if self.group is not None:
                 self.group.step(grad_scale / self.world)
+                self.opt._opt_called = True   # the fused kernel was this step's optimizer.step() (LambdaLR's order check)
             else:
                 flat = self._flat_grad()
                 dist.all_reduce(flat, group=self.pg)

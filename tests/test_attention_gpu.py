@@ -116,3 +116,14 @@ def test_attn_bwd(cfg_name, attn_type):
         # per row: a wrong small-magnitude region (one token's gradient) must not hide behind the global maximum
         rerr = (dqkv[:, sl].float() - ref[:, sl]).norm(dim=1) / (ref[:, sl].norm(dim=1) + 1e-3 * den)
         assert rerr.max().item() < 6e-2, f"{name}: worst row relative error {rerr.max().item()} at row {int(rerr.argmax())}"
+
+
+def test_attn_wide_grid_is_refused_not_approximated():
+    """A 64x64 image grid is outside what the sm_100a kernels tile (the reference fixes 32, task.py:26): the call must
+    fail loudly instead of returning numbers."""
+    cfg = small_config(image_fmap_size=64, heads=2, dim=128)
+    qkv = _qkv(cfg, 1, seed=3)
+    out = torch.zeros(cfg.seq_len, cfg.inner_dim, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(1, cfg.heads, cfg.seq_len, device="cuda")
+    with pytest.raises(RuntimeError):
+        A.attn_fwd(qkv, out, lse, cfg, "axial_row")

@@ -105,6 +105,27 @@ def test_lonely_peer_gives_up_and_keeps_local_values():
         dhts[0].shutdown()
 
 
+def test_peers_with_another_tensor_schema_are_never_grouped():
+    """Two peers average the same model; a third one under the same prefix holds other tensor sizes (a padded layout,
+    another model): it is refused in matchmaking and in the join handshake, and the two keep exact results."""
+    dhts = _dhts(3)
+    try:
+        good = [DecentralizedAverager([torch.full((300,), float(i)), torch.full((7,), float(i))], dhts[i], prefix="t6",
+                                      min_matchmaking_time=1.5, target_group_size=2) for i in range(2)]
+        odd = DecentralizedAverager([torch.full((304,), 9.0), torch.full((3,), 9.0)], dhts[2], prefix="t6",
+                                    min_matchmaking_time=1.5, target_group_size=2)
+        assert good[0].schema == good[1].schema != odd.schema
+        res = _run(good + [odd], [1.0, 1.0, 1.0])
+        assert res[0] is not None and res[1] is not None and res[2] is None
+        for av in good:
+            with av.get_tensors() as ts:
+                assert torch.allclose(ts[0], torch.full((300,), 0.5)) and torch.allclose(ts[1], torch.full((7,), 0.5))
+        with odd.get_tensors() as ts:
+            assert torch.equal(ts[0], torch.full((304,), 9.0))
+    finally:
+        [d.shutdown() for d in dhts]
+
+
 def test_state_download_from_highest_priority_donor():
     dhts = _dhts(3)
     try:
