@@ -17,6 +17,10 @@
 
 namespace b200 {
 
+int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols,
+                      uint32_t box_rows);
+int make_tmap_bf16_nd(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box);
 int attn_make_maps(const void* qkv, const AttnGeom& g, int mode, CUtensorMap* t128, CUtensorMap* ttail,
                    CUtensorMap* taux);
 int attn3_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int T, int F, int mode, cudaStream_t st);
