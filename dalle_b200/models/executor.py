@@ -256,7 +256,9 @@ class Engine:
         G.gemm(G.NT, G.EPI_RESID, u, self.w(m.ff_w2[f]), dst, out2=o, bias=m.ff_b2[f],
                scale=m.scale_g[i].view(-1), res=dst if res is None else res, alpha=alpha)
 
-    def run_stack(self, ids: torch.Tensor, b: _Buffers):
+    def run_stack(self, ids: torch.Tensor, b: _Buffers, after_attention=None):
+        """``after_attention(i, qkv)`` (inference only) is called once the attention half of layer i has run, with
+        the layer's rotated q/k/v rows still in the work buffer - the decode engine fills its K/V cache from it."""
         cfg = self.cfg
         saved = b.saved
         if not saved:
@@ -272,6 +274,8 @@ class Engine:
                 c1, c2 = s.x1, s.x2          # (the last stored layer's are b.x1 / b.x2)
             else:
                 self._f_forward(i, b, b.x2, b.x1, 1.0)
+                if after_attention is not None:
+                    after_attention(i, b.qkv)
                 self._g_forward(i, b, b.x1, b.x2, 1.0)
 
     # ------------------------------------------------------------------------------------------

@@ -95,3 +95,153 @@ def test_sampler_filters_then_applies_temperature(temperature, top_p):
     freq = torch.bincount(codes[:, 0].cpu(), minlength=n).float() / trials
     assert freq[want == 0].sum().item() == 0.0, "drew a token outside the nucleus of the raw logits"
     assert (freq - want).abs().max().item() < 0.03
+
+
+# ---- second-generation decode path (ops/csrc/decode2.cu) -------------------------------------------------------------
+def _ttt_like():
+    return DalleConfig(num_text_tokens=500, text_seq_len=31, dim=1024, depth=1, heads=16, dim_head=64,
+                       image_fmap_size=16, num_image_tokens=512, attn_types=("axial_row",), shared_attn_ids=(0,),
+                       shared_ff_ids=(0,))
+
+
+def _skinny(kind, W, N, K, **kw):
+    """One b200_decode2_gemm call with the keyword arguments of DecodeEngine._gemm, on bare tensors."""
+    from dalle_b200.ops import lib
+
+    L = lib.cuda_lib()
+    ptr = lambda t: None if t is None else t.data_ptr()
+    g = lambda k: kw.get(k)
+    rc = L.b200_decode2_gemm(kind, W.data_ptr(), N, K, ptr(g("xin")), ptr(g("x")), ptr(g("stats")), ptr(g("ln_w")),
+                             ptr(g("ln_b")), ptr(g("ring")), g("pos").data_ptr(), g("T") or 32, g("F") or 16, 1e-5,
+                             ptr(g("bias")), ptr(g("scale")), ptr(g("xout")), ptr(g("stats_out")), ptr(g("out")),
+                             g("ldo") or 0, ptr(g("rot")), g("q_cols") or 0, g("q_scale") or 1.0,
+                             torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, rc
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("N,K", [(1024, 1024), (1024, 4096), (256, 256), (8192, 1024)])
+def test_skinny_gemm_residual_and_logits(N, K):
+    """TMA-operand forms at the production shapes (out-proj K=1024 / 8 splits of 128, FF2 K=4096 / 8 splits of 512, the
+    head N=8192) against fp32 matmul; the residual form also leaves the row statistics of its result behind."""
+    g = torch.Generator(device="cuda").manual_seed(N + K)
+    W = (torch.randn(N, K, device="cuda", generator=g) * K ** -0.5).to(torch.bfloat16)
+    xin = torch.zeros(32, K, device="cuda", dtype=torch.bfloat16)
+    xin[:29] = torch.randn(29, K, device="cuda", generator=g).to(torch.bfloat16)
+    bias = torch.randn(N, device="cuda", generator=g)
+    scale = torch.rand(N, device="cuda", generator=g) + 0.5
+    pos = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ref = xin.float() @ W.float().t() + bias
+    x0 = torch.randn(32, N, device="cuda", generator=g)
+    xout = x0.clone()
+    stats = torch.zeros(32, 2, device="cuda")
+    _skinny(1, W, N, K, xin=xin, bias=bias, scale=scale, xout=xout, stats_out=stats, pos=pos)
+    want = x0 + scale * ref
+    assert (xout - want).abs().max().item() < 2e-2
+    assert torch.allclose(stats[:, 0], xout.sum(1), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(stats[:, 1], (xout * xout).sum(1), rtol=1e-4, atol=1e-2)
+    out = torch.zeros(32, N, device="cuda", dtype=torch.bfloat16)
+    _skinny(3, W, N, K, xin=xin, bias=bias, out=out, ldo=N, pos=pos)
+    assert (out.float() - ref).abs().max().item() < 3e-2 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("D", [1024, 256])
+@pytest.mark.parametrize("pos_kind", ["text", "image_first_col", "image_inner"])
+def test_skinny_gemm_layernorm_prologue(D, pos_kind):
+    """QKV (rotary epilogue) and GEGLU forms: layer norm from the (sum, sum of squares) left by the producer, token
+    shift from the 64-slot ring, against the same statement in fp32 PyTorch."""
+    from dalle_b200.models.rotary import rotary_pair_table
+
+    cfg = DalleConfig(num_text_tokens=500, text_seq_len=31, dim=D, depth=1, heads=D // 64, dim_head=64,
+                      image_fmap_size=16, num_image_tokens=512, attn_types=("axial_row",), shared_attn_ids=(0,),
+                      shared_ff_ids=(0,))
+    T, F = cfg.text_len, cfg.image_fmap_size
+    p = {"text": 9, "image_first_col": T + 3 * F, "image_inner": T + 3 * F + 5}[pos_kind]
+    g = torch.Generator(device="cuda").manual_seed(D + p)
+    x = torch.zeros(32, D, device="cuda")
+    x[:30] = torch.randn(30, D, device="cuda", generator=g) * 2 + 0.3
+    stats = torch.stack((x.sum(1), (x * x).sum(1)), dim=1).contiguous()
+    ln_w, ln_b = torch.rand(D, device="cuda", generator=g) + 0.5, torch.randn(D, device="cuda", generator=g) * 0.1
+    ring = (torch.randn(32, 64, D // 2, device="cuda", generator=g)).to(torch.bfloat16)
+    ring0 = ring.clone()
+    pos = torch.full((1,), p, dtype=torch.int32, device="cuda")
+    # oracle of the prologue
+    hn = torch.nn.functional.layer_norm(x, (D,), ln_w, ln_b, 1e-5)
+    h = hn.clone()
+    if p < T:
+        src_a = src_b = p - 1
+    else:
+        r, c = divmod(p - T, F)
+        src_a = p - F if r >= 1 else -1
+        src_b = p - 1 if c >= 1 else -1
+    h[:, : D // 4] = ring0[:, src_a % 64, : D // 4].float() if src_a >= 0 else 0.0
+    h[:, D // 4: D // 2] = ring0[:, src_b % 64, D // 4: D // 2].float() if src_b >= 0 else 0.0
+    hb = h.to(torch.bfloat16).float()
+    # --- QKV + rotary
+    I = D
+    Wq = (torch.randn(3 * I, D, device="cuda", generator=g) * D ** -0.5).to(torch.bfloat16)
+    rot = rotary_pair_table(cfg).cuda()
+    out = torch.zeros(32, 3 * I, device="cuda", dtype=torch.bfloat16)
+    _skinny(0, Wq, 3 * I, D, x=x, stats=stats, ln_w=ln_w, ln_b=ln_b, ring=ring, pos=pos, T=T, F=F, out=out, ldo=3 * I,
+            rot=rot, q_cols=I, q_scale=0.125)
+    raw = (hb @ Wq.float().t()).view(32, 3 * I // 2, 2)
+    cs = rot[p].repeat(3 * I // 64, 1)                       # [pairs of the row, 2]
+    ref = torch.stack((raw[..., 0] * cs[:, 0] - raw[..., 1] * cs[:, 1], raw[..., 1] * cs[:, 0] + raw[..., 0] * cs[:, 1]),
+                      dim=-1).view(32, 3 * I)
+    ref[:, :I] *= 0.125
+    assert (out.float() - ref).abs().max().item() < 3e-2 * max(1.0, ref.abs().max().item())
+    # the token's own normalised first half went into the ring, other slots untouched
+    assert (ring[:, p % 64].float() - hn[:, : D // 2]).abs().max().item() < 3e-2
+    keep = [s for s in range(64) if s != p % 64]
+    assert torch.equal(ring[:, keep], ring0[:, keep])
+    # --- GEGLU
+    hid = 4 * D
+    W1 = (torch.randn(2 * hid, D, device="cuda", generator=g) * D ** -0.5).to(torch.bfloat16)
+    b1 = torch.randn(2 * hid, device="cuda", generator=g) * 0.1
+    u = torch.zeros(32, hid, device="cuda", dtype=torch.bfloat16)
+    ring.copy_(ring0)
+    _skinny(2, W1, hid, D, x=x, stats=stats, ln_w=ln_w, ln_b=ln_b, ring=ring, pos=pos, T=T, F=F, bias=b1, out=u, ldo=hid)
+    pre = hb @ W1.float().t() + b1
+    ref_u = pre[:, :hid] * torch.nn.functional.gelu(pre[:, hid:])
+    assert (u.float() - ref_u).abs().max().item() < 3e-2 * max(1.0, ref_u.abs().max().item())
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_decode2_prefill_and_stepwise_prompt_agree_with_the_oracle(use_graph):
+    from dalle_b200.models.decode_engine import DecodeEngine, DecodeEngineV1
+
+    cfg = _cfg()
+    torch.manual_seed(0)
+    model = DALLE(cfg, seed=0)
+    with torch.no_grad():
+        for p in list(model.scale_f) + list(model.scale_g):
+            p.fill_(0.3)
+        model.emb_weight.mul_(4.0)
+    model.cuda()
+    text = torch.randint(1, cfg.num_text_tokens, (3, cfg.text_seq_len), device="cuda")
+    eng = DecodeEngine(model, 3)
+    assert not isinstance(eng, DecodeEngineV1)
+    ref = G.generate_codes_reference(model, text, top_k=1, use_cache=True, dtype=torch.float32)
+    a = eng.generate(text, temperature=1.0, top_k=1, use_graph=use_graph, prefill=True)
+    b = eng.generate(text, temperature=1.0, top_k=1, use_graph=False, prefill=False)
+    assert torch.equal(a[:, :32], ref[:, :32]), (a[:, :32], ref[:, :32])
+    assert torch.equal(b[:, :32], ref[:, :32]), (b[:, :32], ref[:, :32])
+    assert (a == ref).float().mean().item() > 0.5
+    assert eng.cache_bytes() < 0.5 * 2 * cfg.depth * 3 * cfg.heads * cfg.seq_len * 64 * 2   # under half of dense
+
+
+def test_first_generation_engine_still_matches():
+    from dalle_b200.models.decode_engine import DecodeEngineV1
+
+    cfg = _cfg()
+    torch.manual_seed(0)
+    model = DALLE(cfg, seed=0)
+    with torch.no_grad():
+        for p in list(model.scale_f) + list(model.scale_g):
+            p.fill_(0.3)
+        model.emb_weight.mul_(4.0)
+    model.cuda()
+    text = torch.randint(1, cfg.num_text_tokens, (3, cfg.text_seq_len), device="cuda")
+    ref = G.generate_codes_reference(model, text, top_k=1, use_cache=True, dtype=torch.float32)
+    codes = DecodeEngineV1(model, 3).generate(text, temperature=1.0, top_k=1)
+    assert torch.equal(codes[:, :32], ref[:, :32])
