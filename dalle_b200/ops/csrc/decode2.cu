@@ -80,6 +80,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   __shared__ __align__(8) uint64_t bar_k[DG_MAX_KB];
   __shared__ __align__(8) uint64_t bar_mma;
   __shared__ uint32_t tmem_slot;
+  __shared__ float s_mean[DG_NB], s_rstd[DG_NB];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dg_smem_raw) + 1023) & ~uintptr_t(1023));
   const int tid = threadIdx.x, warp = tid >> 5;
   const int nkb = a.ks >> 6;
@@ -116,12 +117,17 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       for (int kb = 0; kb < nkb; ++kb) tma_load_2d(sX + kb * 4096, &tmX, &bar_k[kb], k0 + kb * 64, 0);
   } else {
     // ---- layer norm + token shift of this CTA's K slice, written as the 128B-swizzled B tile ----
-    const int b = tid >> 2, q = tid & 3;
+    // thread <-> one 16-byte chunk (8 channels) of the slice and every (128 / chunks)-th row: the norm weights are
+    // loaded once per thread, a warp reads whole contiguous pieces of a row, and the loads of eight rows are in
+    // flight together (the kernel is a latency chain: the first version walked 8 dependent round trips here).
     const int pos = __ldg(a.pos_ptr);
-    const float invK = 1.0f / a.K;
-    const float mean = a.stats_in[b * 2] * invK;
-    const float var = fmaxf(a.stats_in[b * 2 + 1] * invK - mean * mean, 0.f);
-    const float rstd = rsqrtf(var + a.eps);
+    if (tid < 32) {
+      const float invK = 1.0f / a.K;
+      const float2 st = *reinterpret_cast<const float2*>(a.stats_in + tid * 2);
+      const float mean = st.x * invK;
+      s_mean[tid] = mean;
+      s_rstd[tid] = rsqrtf(fmaxf(st.y * invK - mean * mean, 0.f) + a.eps);
+    }
     int src_a = -1, src_b = -1;     // positions feeding channels [0, K/4) and [K/4, K/2)
     if (pos < a.T) {
       src_a = src_b = pos - 1;      // (-1 at the first position)
@@ -131,29 +137,49 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       src_b = c >= 1 ? pos - 1 : -1;
     }
     const int halfK = a.K >> 1, quartK = a.K >> 2;
-    const int per = a.ks >> 2;      // columns of the slice per thread (multiple of 8)
-    for (int c = q * per; c < (q + 1) * per; c += 8) {
-      const int gc = k0 + c;
-      const float4 x0 = *reinterpret_cast<const float4*>(a.x + static_cast<long long>(b) * a.K + gc);
-      const float4 x1 = *reinterpret_cast<const float4*>(a.x + static_cast<long long>(b) * a.K + gc + 4);
-      const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.ln_w + gc));
-      const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.ln_w + gc + 4));
-      const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.ln_b + gc));
-      const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.ln_b + gc + 4));
-      uint4 o;
-      o.x = pack_bf16x2((x0.x - mean) * rstd * w0.x + b0.x, (x0.y - mean) * rstd * w0.y + b0.y);
-      o.y = pack_bf16x2((x0.z - mean) * rstd * w0.z + b0.z, (x0.w - mean) * rstd * w0.w + b0.w);
-      o.z = pack_bf16x2((x1.x - mean) * rstd * w1.x + b1.x, (x1.y - mean) * rstd * w1.y + b1.y);
-      o.w = pack_bf16x2((x1.z - mean) * rstd * w1.z + b1.z, (x1.w - mean) * rstd * w1.w + b1.w);
-      if (gc < halfK) {
-        __nv_bfloat16* rrow = a.ring + (static_cast<long long>(b) * 64) * halfK + gc;
-        if (mt == 0) *reinterpret_cast<uint4*>(rrow + static_cast<long long>(pos & 63) * halfK) = o;
-        const int src = gc < quartK ? src_a : src_b;
-        o = src >= 0 ? *reinterpret_cast<const uint4*>(rrow + static_cast<long long>(src & 63) * halfK)
-                     : make_uint4(0u, 0u, 0u, 0u);
+    const int nch = a.ks >> 3;                       // chunks per row of the slice: 8 .. 64
+    const int ch = tid % nch, r0 = tid / nch;
+    const int rstep = DG_THREADS / nch, nrows = DG_NB / rstep;
+    const int gc = k0 + ch * 8;
+    const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.ln_w + gc));
+    const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.ln_w + gc + 4));
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.ln_b + gc));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.ln_b + gc + 4));
+    const bool shifted = gc < halfK;
+    const int src = gc < quartK ? src_a : src_b;
+    __syncthreads();                                 // s_mean / s_rstd
+    for (int j0 = 0; j0 < nrows; j0 += 8) {
+      float4 xa[8], xb[8];
+      uint4 rg[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int r = r0 + (j0 + u) * rstep;
+        if (j0 + u < nrows) {
+          xa[u] = *reinterpret_cast<const float4*>(a.x + static_cast<long long>(r) * a.K + gc);
+          xb[u] = *reinterpret_cast<const float4*>(a.x + static_cast<long long>(r) * a.K + gc + 4);
+          rg[u] = (shifted && src >= 0)
+                      ? *reinterpret_cast<const uint4*>(a.ring + (static_cast<long long>(r) * 64 + (src & 63)) * halfK + gc)
+                      : make_uint4(0u, 0u, 0u, 0u);
+        }
       }
-      const int kb = c >> 6, ch = (c & 63) >> 3;
-      *reinterpret_cast<uint4*>(sX + kb * 4096 + b * 128 + ((ch ^ (b & 7)) << 4)) = o;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int r = r0 + (j0 + u) * rstep;
+        if (j0 + u < nrows) {
+          const float mean = s_mean[r], rstd = s_rstd[r];
+          uint4 o;
+          o.x = pack_bf16x2((xa[u].x - mean) * rstd * w0.x + b0.x, (xa[u].y - mean) * rstd * w0.y + b0.y);
+          o.y = pack_bf16x2((xa[u].z - mean) * rstd * w0.z + b0.z, (xa[u].w - mean) * rstd * w0.w + b0.w);
+          o.z = pack_bf16x2((xb[u].x - mean) * rstd * w1.x + b1.x, (xb[u].y - mean) * rstd * w1.y + b1.y);
+          o.w = pack_bf16x2((xb[u].z - mean) * rstd * w1.z + b1.z, (xb[u].w - mean) * rstd * w1.w + b1.w);
+          if (shifted) {
+            if (mt == 0)
+              *reinterpret_cast<uint4*>(a.ring + (static_cast<long long>(r) * 64 + (pos & 63)) * halfK + gc) = o;
+            o = rg[u];
+          }
+          *reinterpret_cast<uint4*>(sX + (ch >> 3) * 4096 + r * 128 + (((ch & 7) ^ (r & 7)) << 4)) = o;
+        }
+      }
     }
     fence_proxy_async_smem();
   }
@@ -174,6 +200,26 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
     umma_commit(&bar_mma);
   }
+  // epilogue operands of this thread's first (usually only) group of features: requested now, so that their L2
+  // round trip runs under the MMAs and the cluster exchange instead of after them
+  const int b = tid >> 2, fq = tid & 3;
+  const int own = (EPI == DG_GEGLU ? 64 : 128) / a.ksplit;
+  const int n_first = mt * (EPI == DG_GEGLU ? 64 : 128) + static_cast<int>(ksr) * own + 4 * fq;
+  float4 pre0 = make_float4(0.f, 0.f, 0.f, 0.f), pre1 = pre0, pre2 = pre0;
+  if (n_first < a.N) {
+    if (EPI == DG_GEGLU) {
+      pre0 = __ldg(reinterpret_cast<const float4*>(a.bias + n_first));
+      pre1 = __ldg(reinterpret_cast<const float4*>(a.bias + a.N + n_first));
+    } else if (EPI == DG_RESID) {
+      pre0 = __ldg(reinterpret_cast<const float4*>(a.bias + n_first));
+      pre1 = __ldg(reinterpret_cast<const float4*>(a.scale + n_first));
+      pre2 = *reinterpret_cast<const float4*>(a.xout + static_cast<long long>(b) * a.N + n_first);
+    } else if (EPI == DG_QKV) {
+      const float2* rt = a.rot + static_cast<long long>(__ldg(a.pos_ptr)) * 32 + ((n_first & 63) >> 1);
+      const float2 c0 = __ldg(rt), c1 = __ldg(rt + 1);
+      pre0 = make_float4(c0.x, c0.y, c1.x, c1.y);
+    }
+  }
   __syncwarp();
   mbar_wait(&bar_mma, 0);
   tc_fence_after();
@@ -188,7 +234,6 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   cluster_sync_all();        // every CTA's partial tile is in its shared memory
 
   // ---- reduce over the K splits and finish: this CTA owns 128 / ksplit of the tile's features ----
-  const int b = tid >> 2, fq = tid & 3;
   if (EPI == DG_GEGLU) {
     const int nj = 64 / a.ksplit;
     for (int g = 0; g < nj / 16; ++g) {
@@ -202,8 +247,8 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       }
       const int n = mt * 64 + j;
       if (n < a.N) {
-        const float4 bv = __ldg(reinterpret_cast<const float4*>(a.bias + n));
-        const float4 bg = __ldg(reinterpret_cast<const float4*>(a.bias + a.N + n));
+        const float4 bv = g == 0 ? pre0 : __ldg(reinterpret_cast<const float4*>(a.bias + n));
+        const float4 bg = g == 0 ? pre1 : __ldg(reinterpret_cast<const float4*>(a.bias + a.N + n));
         auto act = [](float v, float gt) { return v * (0.5f * gt * (1.0f + erff(gt * 0.70710678118654752f))); };
         uint2 o;
         o.x = pack_bf16x2(act(val.x + bv.x, gat.x + bg.x), act(val.y + bv.y, gat.y + bg.y));
@@ -224,19 +269,22 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       const int n = mt * 128 + f;
       if (n >= a.N) continue;
       if (EPI == DG_QKV) {
-        const int pos = __ldg(a.pos_ptr);
-        const float2* rt = a.rot + static_cast<long long>(pos) * 32 + ((n & 63) >> 1);
-        const float2 c0 = __ldg(rt), c1 = __ldg(rt + 1);
+        float2 c0 = make_float2(pre0.x, pre0.y), c1 = make_float2(pre0.z, pre0.w);
+        if (g != 0) {
+          const float2* rt = a.rot + static_cast<long long>(__ldg(a.pos_ptr)) * 32 + ((n & 63) >> 1);
+          c0 = __ldg(rt);
+          c1 = __ldg(rt + 1);
+        }
         const float s = n < a.q_cols ? a.q_scale : 1.0f;
         uint2 o;
         o.x = pack_bf16x2((acc.x * c0.x - acc.y * c0.y) * s, (acc.y * c0.x + acc.x * c0.y) * s);
         o.y = pack_bf16x2((acc.z * c1.x - acc.w * c1.y) * s, (acc.w * c1.x + acc.z * c1.y) * s);
         *reinterpret_cast<uint2*>(a.out + static_cast<long long>(b) * a.ldo + n) = o;
       } else if (EPI == DG_RESID) {
-        const float4 bi = __ldg(reinterpret_cast<const float4*>(a.bias + n));
-        const float4 sc = __ldg(reinterpret_cast<const float4*>(a.scale + n));
+        const float4 bi = g == 0 ? pre0 : __ldg(reinterpret_cast<const float4*>(a.bias + n));
+        const float4 sc = g == 0 ? pre1 : __ldg(reinterpret_cast<const float4*>(a.scale + n));
         float4* xp = reinterpret_cast<float4*>(a.xout + static_cast<long long>(b) * a.N + n);
-        float4 xo = *xp;
+        float4 xo = g == 0 ? pre2 : *xp;
         xo.x += sc.x * (acc.x + bi.x); xo.y += sc.y * (acc.y + bi.y);
         xo.z += sc.z * (acc.z + bi.z); xo.w += sc.w * (acc.w + bi.w);
         *xp = xo;
