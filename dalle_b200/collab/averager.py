@@ -61,17 +61,23 @@ class MatchmakingException(Exception):
 
 class GroupInfo:
     def __init__(self, group_id: bytes, peer_ids: List[bytes], endpoints: List[Optional[Tuple[str, int]]],
-                 modes: List[int], gathered: List[Any]):
+                 modes: List[int], gathered: List[Any], bulk_ports: Optional[List[Optional[int]]] = None):
         self.group_id, self.peer_ids, self.endpoints, self.modes, self.gathered = group_id, peer_ids, endpoints, modes, gathered
+        self.bulk_ports = list(bulk_ports) if bulk_ports is not None else [None] * len(peer_ids)
 
     def to_msg(self):
         return {"gid": self.group_id, "pids": self.peer_ids, "eps": [list(e) if e else None for e in self.endpoints],
-                "modes": self.modes, "gathered": self.gathered}
+                "modes": self.modes, "gathered": self.gathered, "bulk": self.bulk_ports}
 
     @classmethod
     def from_msg(cls, m):
         return cls(m["gid"], list(m["pids"]), [tuple(e) if e else None for e in m["eps"]], list(m["modes"]),
-                   list(m["gathered"]))
+                   list(m["gathered"]), m.get("bulk"))
+
+    def native_data_plane(self) -> bool:
+        """Every member that owns a span (everyone but clients) listens on the C++ bulk transport and every member
+        speaks it (clients declare 0): the round can run in b200h_allreduce_round."""
+        return all(b is not None and (b > 0 or m == AveragingMode.CLIENT) for b, m in zip(self.bulk_ports, self.modes))
 
     @property
     def size(self):
@@ -226,6 +232,22 @@ class DecentralizedAverager:
         self._mm_lock: Optional[asyncio.Lock] = None
         self._declare_task = None
         self.last_group: Optional[GroupInfo] = None
+        # C++ data plane of the all-reduce (native/allreduce_pipe.cpp): one persistent listener per averager; its
+        # port travels with the matchmaking record.  DALLE_B200_NATIVE_ALLREDUCE=0 keeps the asyncio part loop.
+        self._bulk_listener = None
+        self._bulk_port: Optional[int] = None
+        if _bulk_available() and os.environ.get("DALLE_B200_NATIVE_ALLREDUCE", "1") != "0":
+            if self.client_mode:
+                self._bulk_port = 0
+            else:
+                from ..transport.bulk import BulkListener
+
+                try:
+                    self._bulk_listener = BulkListener(dht.p2p.endpoint[0] if dht.p2p.endpoint else "127.0.0.1", 0)
+                    self._bulk_port = self._bulk_listener.port
+                except OSError:
+                    self._bulk_listener = None
+        self.native_rounds = 0
         p2p = dht.p2p
         p2p.add_stream_handler(f"{prefix}.join", self._rpc_join)
         p2p.add_stream_handler(f"{prefix}.allreduce", self._rpc_allreduce)
@@ -246,6 +268,9 @@ class DecentralizedAverager:
     def shutdown(self):
         if self._declare_task is not None:
             self._declare_task.cancel()
+        if self._bulk_listener is not None:
+            self._bulk_listener.close()
+            self._bulk_listener = None
 
     # ---- step -----------------------------------------------------------------------------------
     def step(self, gather: Any = None, weight: Optional[float] = None, timeout: Optional[float] = None,
@@ -289,7 +314,8 @@ class DecentralizedAverager:
     def _my_info(self, gather, deadline):
         ep = self.dht.p2p.endpoint
         return {"pid": self.dht.peer_id.raw, "ep": list(ep) if ep else None, "mode": int(self.mode),
-                "deadline": deadline, "gather": gather, "bw": self.bandwidth, "schema": self.schema}
+                "deadline": deadline, "gather": gather, "bw": self.bandwidth, "schema": self.schema,
+                "bulk": self._bulk_port}
 
     def _warn_schema(self, who: bytes, theirs):
         if who not in self._schema_warned:
@@ -359,7 +385,7 @@ class DecentralizedAverager:
         members.sort(key=lambda m: bytes(m["pid"]))
         group = GroupInfo(os.urandom(16), [bytes(m["pid"]) for m in members],
                           [tuple(m["ep"]) if m["ep"] else None for m in members], [m["mode"] for m in members],
-                          [m["gather"] for m in members])
+                          [m["gather"] for m in members], [m.get("bulk") for m in members])
         if not self._assembled.done():
             self._assembled.set_result(group)
         self._looking = False
@@ -422,6 +448,8 @@ class DecentralizedAverager:
         return self._partition.assign(owner_w)
 
     async def _run_allreduce(self, group: GroupInfo, weight: float):
+        if group.native_data_plane() and (self._bulk_listener is not None or self.client_mode):
+            return await self._run_allreduce_native(group, weight)
         me = group.peer_ids.index(self.dht.peer_id.raw)
         spans = self._spans(group)
         parts = self._partition.parts
@@ -450,6 +478,47 @@ class DecentralizedAverager:
         finally:
             # keep serving late senders for a moment, then forget the round
             asyncio.get_event_loop().call_later(5.0, self._rounds.pop, group.group_id, None)
+
+    _CODEC_IDS = {"none": 0, "fp16": 1, "uniform8": 2, "u8": 2}
+
+    async def _run_allreduce_native(self, group: GroupInfo, weight: float):
+        """The whole round in C++ threads (native/allreduce_pipe.cpp): this coroutine only builds the descriptor and
+        waits for the call in a worker thread, with the GIL released."""
+        import ctypes
+
+        from ..native import host
+
+        me = group.peer_ids.index(self.dht.peer_id.raw)
+        n, parts, spans = group.size, self._partition.parts, self._spans(group)
+        comp = self.compression
+
+        def codec_id(tensor_numel):
+            c = comp.choose(tensor_numel) if isinstance(comp, C.SizeAdaptiveCompression) else comp
+            return self._CODEC_IDS[c.name]
+
+        I, LL = ctypes.c_int, ctypes.c_longlong
+        modes = (I * n)(*[int(m) for m in group.modes])
+        hosts = (ctypes.c_char_p * n)(*[(ep[0].encode() if ep else None) for ep in group.endpoints])
+        ports = (I * n)(*[int(b or 0) for b in group.bulk_ports])
+        sb, se = (I * n)(*[s[0] for s in spans]), (I * n)(*[s[1] for s in spans])
+        ps, pe = (LL * len(parts))(*[p[0] for p in parts]), (LL * len(parts))(*[p[1] for p in parts])
+        pc = (I * len(parts))(*[codec_id(p[2]) for p in parts])
+        failed = (I * n)()
+        gid = (ctypes.c_ubyte * 16)(*group.group_id[:16])
+        desc = host.AllreduceDesc(n, me, modes, hosts, ports, sb, se, len(parts), ps, pe, pc, self._flat.data_ptr(),
+                                  float(weight), gid, self._bulk_listener._l if self._bulk_listener else None,
+                                  int(1000 * self.sender_timeout), failed)
+        def run():
+            with self.lock_averaged_tensors:      # the round reads and updates the buffer in place
+                return host.allreduce_round(desc)
+
+        rc = await asyncio.get_event_loop().run_in_executor(None, run)
+        self.native_rounds += 1
+        if rc < 0:
+            raise AllreduceException(f"native all-reduce setup failed ({rc})")
+        n_exchanges = sum(1 for k in range(n) if k != me and (spans[k][1] > spans[k][0] or group.modes[k] != AveragingMode.AUX))
+        if rc > 0 and sum(failed) >= max(1, n_exchanges):
+            raise AllreduceException(f"every exchange of the round failed ({list(failed)})")
 
     async def _reduce_own_span(self, rnd: _Round, p0: int, p1: int):
         parts = self._partition.parts

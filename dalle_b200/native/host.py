@@ -12,6 +12,22 @@ _c = ctypes
 _configured = False
 
 
+class AllreduceDesc(_c.Structure):
+    """include/b200_host_api.h B200hAllreduce."""
+    _fields_ = [("n_members", _c.c_int), ("my_index", _c.c_int), ("modes", _c.POINTER(_c.c_int)),
+                ("hosts", _c.POINTER(_c.c_char_p)), ("ports", _c.POINTER(_c.c_int)),
+                ("span_begin", _c.POINTER(_c.c_int)), ("span_end", _c.POINTER(_c.c_int)), ("n_parts", _c.c_int),
+                ("part_start", _c.POINTER(_c.c_longlong)), ("part_end", _c.POINTER(_c.c_longlong)),
+                ("part_codec", _c.POINTER(_c.c_int)), ("flat", _c.c_void_p), ("weight", _c.c_float),
+                ("group_id", _c.POINTER(_c.c_ubyte)), ("listener", _c.c_void_p), ("timeout_ms", _c.c_int),
+                ("failed_out", _c.POINTER(_c.c_int))]
+
+
+def allreduce_round(desc: "AllreduceDesc") -> int:
+    """Blocking; ctypes releases the GIL for the duration of the call."""
+    return int(_h().b200h_allreduce_round(_c.byref(desc)))
+
+
 def available() -> bool:
     return _lib.host_lib_available()
 
@@ -35,6 +51,7 @@ def _h():
         h.b200h_recv_header.argtypes, h.b200h_recv_header.restype = [i, _c.POINTER(_c.c_ulonglong), i], ll
         h.b200h_recv_payload.argtypes, h.b200h_recv_payload.restype = [i, p, ll, i], i
         h.b200h_close.argtypes = [i]
+        h.b200h_allreduce_round.argtypes, h.b200h_allreduce_round.restype = [_c.POINTER(AllreduceDesc)], i
         _configured = True
     return h
 

@@ -28,6 +28,36 @@ long long b200h_recv_header(int fd, unsigned long long* tag, int timeout_ms);
 int b200h_recv_payload(int fd, void* data, long long nbytes, int timeout_ms);
 void b200h_close(int fd);
 
+/* One peer's side of a butterfly all-reduce round, run by C++ threads over the bulk transport (the caller's GIL is
+ * released for the whole call): for every other owner, parts of its span are compressed from `flat` and sent while
+ * the returned deltas are decoded and added in place; for this peer's own span, parts arriving from the other
+ * senders are decoded, accumulated with their weights, averaged when complete, and the per-sender deltas are
+ * compressed and sent back.  Semantics of hivemind's AllReduceRunner / TensorPartReducer: a failing or
+ * late sender is dropped and the part is averaged over the rest; auxiliary members own spans and contribute nothing;
+ * client-mode members contribute and own nothing.
+ * modes: 0 node, 1 client, 2 auxiliary.  part_codec: 0 fp32, 1 fp16 (clamped), 2 uniform 8-bit (hivemind).
+ * Returns the number of exchanges that failed (0 = clean), < 0 on a setup error; failed_out[k] = 1 for every member
+ * whose exchange with this peer broke. */
+typedef struct {
+  int n_members, my_index;
+  const int* modes;
+  const char* const* hosts;
+  const int* ports;
+  const int* span_begin;
+  const int* span_end;
+  int n_parts;
+  const long long* part_start;
+  const long long* part_end;
+  const int* part_codec;
+  float* flat;
+  float weight;
+  const unsigned char* group_id; /* 16 bytes */
+  void* listener;                /* this peer's b200h_listen handle; NULL for a client-mode peer */
+  int timeout_ms;
+  int* failed_out;
+} B200hAllreduce;
+int b200h_allreduce_round(const B200hAllreduce* d);
+
 #ifdef __cplusplus
 }
 #endif

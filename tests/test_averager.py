@@ -41,8 +41,11 @@ def test_partition_regions_and_spans():
     assert spans[1][0] == spans[1][1] and spans[0][1] == spans[2][0] and spans[2][1] == len(p.parts)
 
 
+@pytest.mark.parametrize("plane", ["native", "asyncio"])
 @pytest.mark.parametrize("compression", ["none", "adaptive"])
-def test_weighted_allreduce_three_peers(compression):
+def test_weighted_allreduce_three_peers(compression, plane, monkeypatch):
+    """Both data planes: the C++ thread pipeline (native/allreduce_pipe.cpp) and the asyncio part loop."""
+    monkeypatch.setenv("DALLE_B200_NATIVE_ALLREDUCE", "1" if plane == "native" else "0")
     comp = C.NoCompression() if compression == "none" else C.SizeAdaptiveCompression(
         2 ** 16 + 1, C.Float16Compression(), C.Uniform8BitQuantization())
     dhts = _dhts(3)
@@ -57,6 +60,7 @@ def test_weighted_allreduce_three_peers(compression):
         res = _run(avs, weights)
         assert all(r is not None and len(r) == 3 for r in res), res
         assert {v["i"] for v in res[0].values()} == {0, 1, 2}
+        assert all(a.native_rounds == (1 if plane == "native" else 0) for a in avs), [a.native_rounds for a in avs]
         for k in range(len(shapes)):
             ref = sum(w * d[k] for w, d in zip(weights, data)) / sum(weights)
             for a in avs:
@@ -82,10 +86,37 @@ def test_client_mode_and_aux_peer():
                                      allreduce_timeout=15)]
         res = _run(avs, [1.0, 0.0, 3.0])
         assert all(r is not None for r in res)
+        assert all(a.native_rounds == 1 for a in avs)   # aux owner and client sender both speak the C++ data plane
         ref = (1.0 * 1 + 3.0 * 3) / 4.0   # the auxiliary peer contributes nothing
         for i in (0, 2):
             with avs[i].get_tensors() as ts:
                 assert torch.allclose(ts[0], torch.full((5000,), ref), atol=1e-5)
+    finally:
+        for d in dhts:
+            d.shutdown()
+
+
+def test_native_round_drops_a_sender_with_non_finite_values_and_averages_the_rest():
+    """hivemind's reducer bans a sender whose part is malformed and finishes with the others: the C++ owner refuses a
+    part with Inf in it, the two healthy peers still converge to their own mean on that span."""
+    dhts = _dhts(3)
+    try:
+        data = [[torch.full((4000,), 1.0)], [torch.full((4000,), 3.0)], [torch.full((4000,), float("inf"))]]
+        avs = [DecentralizedAverager(data[i], dhts[i], prefix="t7", min_matchmaking_time=2.0, target_group_size=3,
+                                     allreduce_timeout=15, sender_timeout=3.0, part_size_bytes=2 ** 12) for i in range(3)]
+        res = _run(avs, [1.0, 1.0, 1.0])
+        assert res[0] is not None and res[1] is not None
+        assert all(a.native_rounds == 1 for a in avs)
+        own = [a._spans(a.last_group or avs[0].last_group) for a in avs[:1]][0]
+        parts = avs[0]._partition.parts
+        bad_owner = avs[0].last_group.peer_ids.index(dhts[2].peer_id.raw)
+        for i in (0, 1):
+            with avs[i].get_tensors() as ts:
+                for k, (q0, q1) in enumerate(own):
+                    if k == bad_owner or q1 <= q0:
+                        continue   # the span reduced BY the bad peer carries its own Inf; the others must be clean
+                    s, e = parts[q0][0], parts[q1 - 1][1]
+                    assert torch.allclose(ts[0][s:e], torch.full((e - s,), 2.0), atol=1e-5), (i, k, ts[0][s:e][:4])
     finally:
         for d in dhts:
             d.shutdown()
