@@ -59,6 +59,35 @@ class MatchmakingException(Exception):
     pass
 
 
+class StepControl:
+    """Handle of a pre-scheduled averaging round (hivemind.averaging.control.StepControl): matchmaking starts at once
+    and runs until ``scheduled_time``; the all-reduce itself begins only after ``allow_allreduce()`` - by then the
+    caller has put its final data into the averager and set ``weight``."""
+
+    def __init__(self, weight: float, scheduled_time: Optional[float]):
+        self.weight, self.scheduled_time = float(weight), scheduled_time
+        self._allow, self._cancelled = threading.Event(), threading.Event()
+        self.began_allreduce = False
+        self.future = None
+
+    def allow_allreduce(self):
+        self._allow.set()
+
+    def cancel(self):
+        self._cancelled.set()
+        self._allow.set()
+
+    @property
+    def cancelled(self) -> bool:
+        return self._cancelled.is_set()
+
+    def done(self) -> bool:
+        return self.future is not None and self.future.done()
+
+    def result(self, timeout: Optional[float] = None):
+        return self.future.result(timeout)
+
+
 class GroupInfo:
     def __init__(self, group_id: bytes, peer_ids: List[bytes], endpoints: List[Optional[Tuple[str, int]]],
                  modes: List[int], gathered: List[Any], bulk_ports: Optional[List[Optional[int]]] = None):
@@ -248,6 +277,7 @@ class DecentralizedAverager:
                 except OSError:
                     self._bulk_listener = None
         self.native_rounds = 0
+        self._round_key: Optional[int] = None
         p2p = dht.p2p
         p2p.add_stream_handler(f"{prefix}.join", self._rpc_join)
         p2p.add_stream_handler(f"{prefix}.allreduce", self._rpc_allreduce)
@@ -274,16 +304,33 @@ class DecentralizedAverager:
 
     # ---- step -----------------------------------------------------------------------------------
     def step(self, gather: Any = None, weight: Optional[float] = None, timeout: Optional[float] = None,
-             allow_retries: bool = True, wait: bool = True, target_group_size: Optional[int] = None):
+             allow_retries: bool = True, wait: bool = True, target_group_size: Optional[int] = None,
+             round_key: Optional[int] = None):
         """Find a group and run one all-reduce.  Returns {peer_id_bytes: gathered} on success, None on failure
-        (the local tensors are then unchanged or partially averaged, never corrupted)."""
+        (the local tensors are then unchanged or partially averaged, never corrupted).  ``round_key`` (for instance
+        the epoch): peers that declare different keys are never grouped; None matches anything (auxiliary peers)."""
         if weight is None:
             weight = float(self.mode != AveragingMode.AUX)
         fut = asyncio.run_coroutine_threadsafe(
-            self._step(gather, float(weight), timeout, allow_retries, target_group_size), self.dht.loop)
+            self._step(gather, float(weight), timeout, allow_retries, target_group_size, None, round_key), self.dht.loop)
         return fut.result() if wait else fut
 
-    async def _step(self, gather, weight, timeout, allow_retries, target_group_size):
+    def schedule_step(self, scheduled_time: Optional[float] = None, gather: Any = None, weight: Optional[float] = None,
+                      timeout: Optional[float] = None, allow_retries: bool = False,
+                      target_group_size: Optional[int] = None, round_key: Optional[int] = None) -> StepControl:
+        """Start looking for a group NOW, aiming to have it assembled at ``scheduled_time`` (DHT time), and hold the
+        all-reduce until ``control.allow_allreduce()`` (reference flag --matchmaking_time, arguments.py:66-68: peers
+        begin matchmaking that many seconds before the tracker's ETA, so the wait overlaps the last micro-batches)."""
+        if weight is None:
+            weight = float(self.mode != AveragingMode.AUX)
+        control = StepControl(weight, scheduled_time)
+        control.future = asyncio.run_coroutine_threadsafe(
+            self._step(gather, float(weight), timeout, allow_retries, target_group_size, control, round_key),
+            self.dht.loop)
+        return control
+
+    async def _step(self, gather, weight, timeout, allow_retries, target_group_size,
+                    control: Optional[StepControl] = None, round_key: Optional[int] = None):
         if self._mm_lock is None:
             self._mm_lock = asyncio.Lock()
         deadline = time.monotonic() + timeout if timeout is not None else None
@@ -292,12 +339,31 @@ class DecentralizedAverager:
             while True:
                 attempt += 1
                 mm_time = self.min_matchmaking_time
+                if control is not None and control.scheduled_time is not None and attempt == 1:
+                    mm_time = max(0.5, control.scheduled_time - get_dht_time())
                 if deadline is not None:
                     mm_time = min(mm_time, max(0.1, deadline - time.monotonic()))
                 try:
+                    if control is not None and control.cancelled:
+                        return None
+                    self._round_key = round_key
+                    t_mm = time.monotonic()
                     group = await self._look_for_group(gather, weight, mm_time, target_group_size or self.target_group_size)
+                    logger.debug(f"{self.prefix}: matchmaking (key {round_key}, window {mm_time:.2f}s, scheduled "
+                                 f"{control is not None}) -> {'group of %d' % group.size if group else 'nobody'} after "
+                                 f"{time.monotonic() - t_mm:.2f}s")
                     if group is None:
                         raise MatchmakingException("no group found")
+                    if control is not None:
+                        # the group exists; the data may not: wait for the owner of this round to release it
+                        while not control._allow.is_set():
+                            if deadline is not None and time.monotonic() >= deadline:
+                                raise asyncio.TimeoutError()
+                            await asyncio.sleep(0.002)
+                        if control.cancelled:
+                            return None
+                        weight = control.weight
+                        control.began_allreduce = True
                     remaining = None if deadline is None else max(0.1, deadline - time.monotonic())
                     ar_timeout = self.allreduce_timeout if remaining is None else (
                         min(self.allreduce_timeout, remaining) if self.allreduce_timeout else remaining)
@@ -306,6 +372,7 @@ class DecentralizedAverager:
                     return {pid: g for pid, g in zip(group.peer_ids, group.gathered)}
                 except (MatchmakingException, AllreduceException, asyncio.TimeoutError, P2PError, ConnectionError,
                         OSError) as e:
+                    logger.debug(f"{self.prefix}: averaging attempt {attempt} failed: {e!r}")
                     if not allow_retries or (deadline is not None and time.monotonic() >= deadline - 0.05):
                         return None
                     await asyncio.sleep(0.05)
@@ -315,7 +382,11 @@ class DecentralizedAverager:
         ep = self.dht.p2p.endpoint
         return {"pid": self.dht.peer_id.raw, "ep": list(ep) if ep else None, "mode": int(self.mode),
                 "deadline": deadline, "gather": gather, "bw": self.bandwidth, "schema": self.schema,
-                "bulk": self._bulk_port}
+                "bulk": self._bulk_port, "rk": self._round_key}
+
+    def _same_round(self, theirs) -> bool:
+        mine = self._round_key
+        return mine is None or theirs is None or int(mine) == int(theirs)
 
     def _warn_schema(self, who: bytes, theirs):
         if who not in self._schema_warned:
@@ -335,6 +406,8 @@ class DecentralizedAverager:
                     if d.get("schema", self.schema) != self.schema:
                         self._warn_schema(bytes(pid), d.get("schema"))
                         continue
+                    if not self._same_round(d.get("rk")):
+                        continue       # that peer is looking for a group for another epoch
                     out.append((d["deadline"], bytes(pid), tuple(d["ep"])))
         return sorted(out)
 
@@ -348,7 +421,8 @@ class DecentralizedAverager:
         try:
             if self.mode != AveragingMode.CLIENT:
                 await self.dht.node.store(f"{self.prefix}.matchmaking",
-                                          {"ep": info["ep"], "deadline": deadline, "schema": self.schema},
+                                          {"ep": info["ep"], "deadline": deadline, "schema": self.schema,
+                                           "rk": self._round_key},
                                           deadline + 1.0, subkey=me)
             tried_at: Dict[bytes, float] = {}
             while True:
@@ -404,6 +478,9 @@ class DecentralizedAverager:
             if payload.get("schema") != self.schema:
                 self._warn_schema(pid, payload.get("schema"))
                 await stream.send({"status": "schema_mismatch", "schema": self.schema})
+                return
+            if not self._same_round(payload.get("rk")):
+                await stream.send({"status": "rejected"})
                 return
             self._followers[pid] = {"info": payload}
             await stream.send({"status": "accepted"})

@@ -36,7 +36,7 @@ from typing import Callable, List, Optional
 import torch
 import torch.distributed as dist
 
-from ..dht import DHT
+from ..dht import DHT, get_dht_time
 from . import compression as C
 from .averager import DecentralizedAverager
 from .optimizer import GradientAverager, TrainingStateAverager, _Callbacks
@@ -188,6 +188,8 @@ class GroupOptimizer:
             self.tracker = _TrackerMirror()
         self._pool = ThreadPoolExecutor(max_workers=1)
         self._pending_state_round: Optional[Future] = None
+        self._scheduled_grads = None       # leader: pre-scheduled gradient round (StepControl)
+        self.scheduled_rounds_used = 0
 
     # ---- surface used by the reference ----------------------------------------------------------
     @property
@@ -362,6 +364,7 @@ class GroupOptimizer:
             behind = self.local_epoch < tr.global_epoch - 1
             if not behind:
                 tr.report_local_progress(self.local_epoch, self.samples)
+                self._maybe_schedule_gradient_averaging()
             fut = self._pending_state_round
             c[0] = float((not behind) and bool(tr.ready_to_update_epoch))
             c[1] = float(tr.global_progress.num_peers > 1 or bool(self._target_group_size))
@@ -386,6 +389,22 @@ class GroupOptimizer:
         if do_global:
             self._global_step(multi_peer)
         return loss
+
+    def _maybe_schedule_gradient_averaging(self):
+        """Leader only: start looking for a swarm group ``matchmaking_time`` before the tracker's ETA of the epoch
+        (same rule as collab.Optimizer; reference arguments.py:66-68), so the search overlaps the last micro-batches."""
+        ctl = self._scheduled_grads
+        if ctl is not None and (ctl.done() or ctl.cancelled):
+            self._scheduled_grads = ctl = None
+        tr = self.tracker
+        if ctl is not None or not (tr.global_progress.num_peers > 1 or self._target_group_size):
+            return
+        eta, now = tr.estimated_next_update_time, get_dht_time()
+        if eta - now <= self.matchmaking_time:
+            self._scheduled_grads = self.grad_averager.schedule_step(
+                scheduled_time=max(eta, now + self.grad_averager.min_matchmaking_time),
+                timeout=self.averaging_timeout + self.matchmaking_time, target_group_size=self._group_size_hint(),
+                round_key=self.local_epoch)
 
     def _group_size_hint(self) -> Optional[int]:
         if self._target_group_size:
@@ -437,13 +456,20 @@ class GroupOptimizer:
                 if self.is_leader:
                     if self.fused:
                         torch.cuda.synchronize()
-                    try:
-                        res = self.grad_averager.step(weight=float(self.samples), reset_accumulators=False,
-                                                      timeout=self.averaging_timeout,
-                                                      target_group_size=self._group_size_hint())
-                        averaged = res is not None
-                    except Exception as e:
-                        logger.warning(f"gradient averaging failed: {e!r}")
+                    ctl, self._scheduled_grads = self._scheduled_grads, None
+                    if ctl is not None and not (ctl.done() or ctl.cancelled):
+                        averaged = self.grad_averager.finish_scheduled_step(
+                            ctl, weight=float(self.samples), timeout=self.averaging_timeout + self.matchmaking_time) is not None
+                        self.scheduled_rounds_used += averaged
+                    if not averaged:
+                        try:
+                            res = self.grad_averager.step(weight=float(self.samples), reset_accumulators=False,
+                                                          timeout=self.averaging_timeout,
+                                                          target_group_size=self._group_size_hint(),
+                                                          round_key=self.local_epoch)
+                            averaged = res is not None
+                        except Exception as e:
+                            logger.warning(f"gradient averaging failed: {e!r}")
                     if averaged:
                         self.grad_averager.put_averaged_grads_into_params_()
                     elif self.verbose:
@@ -533,6 +559,9 @@ class GroupOptimizer:
             self._apply_finished_state_round()
 
     def shutdown(self):
+        if self._scheduled_grads is not None:
+            self._scheduled_grads.cancel()
+            self._scheduled_grads = None
         self._finish_pending()
         if self.is_leader:
             self.tracker.shutdown()

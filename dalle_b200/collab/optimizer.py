@@ -16,6 +16,7 @@ part - the parameter averaging round runs on a background thread and is applied 
 from __future__ import annotations
 
 import logging
+import os
 import threading
 import time
 from concurrent.futures import Future, ThreadPoolExecutor
@@ -25,7 +26,8 @@ import torch
 
 from ..dht import DHT
 from . import compression as C
-from .averager import DecentralizedAverager
+from ..dht import get_dht_time
+from .averager import DecentralizedAverager, StepControl
 from .progress_tracker import ProgressTracker
 
 logger = logging.getLogger(__name__)
@@ -111,6 +113,23 @@ class GradientAverager(DecentralizedAverager):
         self._new_averaged_grads = out is not None
         if reset_accumulators:
             self.reset_accumulated_grads_()
+        return out
+
+    def schedule_step(self, scheduled_time=None, timeout=None, **kwargs) -> StepControl:
+        """Matchmaking now, all-reduce when ``finish_scheduled_step`` releases it (the accumulators keep filling)."""
+        return super().schedule_step(scheduled_time=scheduled_time, timeout=timeout,
+                                     gather={"samples": self.local_samples_accumulated}, **kwargs)
+
+    def finish_scheduled_step(self, control: StepControl, weight: Optional[float] = None, timeout=None):
+        self.load_accumulators_into_averager_()
+        control.weight = float(self.local_samples_accumulated) if weight is None else float(weight)
+        control.allow_allreduce()
+        try:
+            out = control.result(timeout)
+        except Exception:
+            control.cancel()
+            out = None
+        self._new_averaged_grads = out is not None
         return out
 
     @torch.no_grad()
@@ -243,6 +262,9 @@ class Optimizer:
         self._pool = ThreadPoolExecutor(max_workers=1)
         self._pending_state_round: Optional[Future] = None
         self._schema_hash = None
+        # pre-scheduled gradient round: matchmaking starts `matchmaking_time` before the tracker's ETA of the epoch
+        self._scheduled_grads: Optional[StepControl] = None
+        self.scheduled_rounds_used = 0
 
     # ---- surface used by the reference ----------------------------------------------------------
     @property
@@ -312,13 +334,38 @@ class Optimizer:
         if not self.is_synchronized_with_peers():
             logger.info(f"peer is out of sync (local epoch {self.local_epoch}, global {self.tracker.global_epoch}): "
                         f"downloading state")
+            if self._scheduled_grads is not None:
+                self._scheduled_grads.cancel()
+                self._scheduled_grads = None
             self.load_state_from_peers()
             return loss
         self.grad_averager.accumulate_grads_(batch_size)
         self.tracker.report_local_progress(self.local_epoch, self.grad_averager.local_samples_accumulated)
+        self._maybe_schedule_gradient_averaging()
         if self.tracker.ready_to_update_epoch:
             self._update_global_epoch(grad_scaler)
         return loss
+
+    def _maybe_schedule_gradient_averaging(self):
+        """hivemind.Optimizer._maybe_schedule_gradient_averaging: once the tracker expects the swarm to reach the target
+        batch within ``matchmaking_time`` seconds, start looking for a group in the background so that the group is
+        there when the last micro-batch is (reference arguments.py:66-68)."""
+        ctl = self._scheduled_grads
+        if ctl is not None and (ctl.done() or ctl.cancelled):
+            self._scheduled_grads = ctl = None       # failed or gave up before its epoch came: schedule again
+        if ctl is not None or not (self.tracker.global_progress.num_peers > 1 or self._target_group_size):
+            return
+        logger.debug(f"tracker: {self.tracker.global_progress}")
+        eta = self.tracker.estimated_next_update_time
+        now = get_dht_time()
+        if eta - now <= self.matchmaking_time:
+            # (never a shorter window than the un-scheduled path gives: peers notice the epoch at different moments)
+            self._scheduled_grads = self.grad_averager.schedule_step(
+                scheduled_time=max(eta, now + self.grad_averager.min_matchmaking_time),
+                timeout=self.averaging_timeout + self.matchmaking_time,
+                target_group_size=self._group_size_hint(), round_key=self.local_epoch)
+            if self.verbose:
+                logger.info(f"pre-scheduled gradient averaging, group due in {max(eta - now, 0.0):.1f}s")
 
     def _group_size_hint(self) -> Optional[int]:
         if self._target_group_size:
@@ -331,17 +378,28 @@ class Optimizer:
         with self.tracker.pause_updates():
             samples = self.grad_averager.local_samples_accumulated
             averaged = None
-            if self.tracker.global_progress.num_peers > 1 or self._target_group_size:
+            ctl, self._scheduled_grads = self._scheduled_grads, None
+            if ctl is not None and (ctl.done() or ctl.cancelled):
+                ctl = None                           # its matchmaking already ended without a group
+            if ctl is not None:
+                averaged = self.grad_averager.finish_scheduled_step(ctl, weight=float(samples),
+                                                                    timeout=self.averaging_timeout + self.matchmaking_time)
+                self.scheduled_rounds_used += averaged is not None
+                if averaged is None:
+                    logger.warning("the pre-scheduled gradient round found no group; looking again")
+            if averaged is None and (self.tracker.global_progress.num_peers > 1 or self._target_group_size):
                 try:
                     averaged = self.grad_averager.step(weight=float(samples), reset_accumulators=False,
                                                        timeout=self.averaging_timeout,
-                                                       target_group_size=self._group_size_hint())
+                                                       target_group_size=self._group_size_hint(),
+                                                       round_key=self.local_epoch)
                 except Exception as e:
                     logger.warning(f"gradient averaging failed: {e!r}")
-            else:
+            elif averaged is None:
                 self.grad_averager.load_accumulators_into_averager_()
             if averaged is None and self.verbose:
-                logger.info("proceeding with local gradients")
+                logger.info(f"proceeding with local gradients (the tracker sees {self.tracker.global_progress.num_peers} "
+                            f"peer(s), global epoch {self.tracker.global_epoch}, local epoch {self.local_epoch})")
             # averaged (or local, normalised by micro-steps) gradients -> .grad -> wrapped optimizer
             self.grad_averager.put_averaged_grads_into_params_()
             if self._before_local_step is not None:
@@ -414,6 +472,8 @@ class Optimizer:
                                        allow_retries=False)
 
     def shutdown(self):
+        if self._scheduled_grads is not None:
+            self._scheduled_grads.cancel()
         self._finish_pending()
         self.tracker.shutdown()
         self.grad_averager.shutdown()

@@ -43,6 +43,9 @@ class GlobalTrainingProgress:
     next_fetch_time: float
 
 
+_PROCESS_KEY_OWNER: dict = {}   # which DHT node of this process signs with the process-wide key
+
+
 class PerformanceEMA:
     """Exponential moving average of samples/s with bias correction; ``pause`` excludes global-step time."""
 
@@ -94,7 +97,25 @@ class ProgressTracker(threading.Thread):
         self.default_refresh_period = default_refresh_period
         self.expected_drift_peers, self.expected_drift_rate = expected_drift_peers, expected_drift_rate
         self.metadata_expiration = metadata_expiration
-        self.performance_ema = PerformanceEMA(alpha=performance_ema_alpha, paused=True)
+        self.performance_ema = PerformanceEMA(alpha=performance_ema_alpha)
+        if private_key is None:
+            # One signing key per DHT node: the key of a signature validator the node already has (two validators
+            # with different keys would each demand their own envelope), else a fresh one.  Not the process-wide key:
+            # two peers inside one process (tests, notebooks) would publish their progress under the same
+            # [owner:...] sub-key and erase each other's record.
+            private_key = getattr(dht, "_record_signing_key", None)
+            if private_key is None:
+                from ..dht.crypto import RSAPrivateKey
+
+                existing = [v for v in getattr(getattr(dht, "_validator", None), "_validators", [])
+                            if isinstance(v, RSASignatureValidator)]
+                if existing:
+                    private_key = existing[0]._private_key
+                elif _PROCESS_KEY_OWNER.setdefault("dht", id(dht)) == id(dht):
+                    private_key = RSAPrivateKey.process_wide()    # the first node of the process (the usual case)
+                else:
+                    private_key = RSAPrivateKey()
+                dht._record_signing_key = private_key
         sig = RSASignatureValidator(private_key)
         self._local_public_key = sig.local_public_key
         dht.add_validators([SchemaValidator(TrainingProgressSchema, prefix=prefix), sig])

@@ -158,3 +158,42 @@ def test_nan_in_parameters_rolls_back_to_the_local_backup(tmp_path):
         opt.shutdown()
     finally:
         d0.shutdown()
+
+
+def test_matchmaking_is_scheduled_ahead_of_the_epoch_and_overlaps_the_last_micro_batches():
+    """--matchmaking_time (reference arguments.py:66-68): once the tracker expects the target batch within the
+    matchmaking window, the group search runs in the background while micro-batches keep accumulating; the global
+    step then finds its group waiting instead of opening a matchmaking window of its own."""
+    d0 = _dht()
+    d1 = _dht([str(m) for m in d0.get_visible_maddrs()])
+    try:
+        (m0, o0), (m1, o1) = _make(d0, "sched", bs=4, target=160), _make(d1, "sched", bs=4, target=160)
+        waits, errors = {0: [], 1: []}, []
+
+        def train(k, model, opt):
+            try:
+                while opt.local_epoch < 3:
+                    for p in model.parameters():
+                        p.grad = torch.ones_like(p) if p.grad is None else p.grad.add_(1.0)
+                    before, t0 = opt.local_epoch, time.perf_counter()
+                    opt.step()
+                    if opt.local_epoch != before:
+                        waits[k].append(time.perf_counter() - t0)
+                    time.sleep(0.1)       # 20 micro-steps of 0.1 s per peer and epoch: the ETA is seconds away
+            except Exception as e:  # pragma: no cover
+                errors.append(e)
+
+        ts = [threading.Thread(target=train, args=(0, m0, o0)), threading.Thread(target=train, args=(1, m1, o1))]
+        [t.start() for t in ts]
+        [t.join(120) for t in ts]
+        assert not errors, errors
+        assert o0.local_epoch >= 3 and o1.local_epoch >= 3
+        # the first epoch has no speed estimate yet; afterwards rounds are pre-scheduled and were actually used
+        assert o0.scheduled_rounds_used >= 1 and o1.scheduled_rounds_used >= 1, (o0.scheduled_rounds_used, o1.scheduled_rounds_used)
+        # ... and a global step that found its group waiting is much shorter than the 1.5 s matchmaking window
+        assert min(waits[0][1:] + waits[1][1:]) < 1.0, waits
+        o0._finish_pending(); o1._finish_pending()
+        assert torch.allclose(m0.weight, m1.weight, atol=1e-4)
+        o0.shutdown(); o1.shutdown()
+    finally:
+        d0.shutdown(); d1.shutdown()
