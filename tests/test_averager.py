@@ -53,7 +53,7 @@ def test_weighted_allreduce_three_peers(compression, plane, monkeypatch):
         g = torch.Generator().manual_seed(0)
         shapes = [(300,), (70, 1000), (17,)]
         data = [[torch.randn(*s, generator=g) for s in shapes] for _ in range(3)]
-        avs = [DecentralizedAverager(data[i], dhts[i], prefix="t1", min_matchmaking_time=2.0, target_group_size=3,
+        avs = [DecentralizedAverager(data[i], dhts[i], prefix="t1", min_matchmaking_time=4.0, target_group_size=3,
                                      compression=comp, part_size_bytes=2 ** 16, allreduce_timeout=15, start=True)
                for i in range(3)]
         weights = [1.0, 2.0, 5.0]
