@@ -121,3 +121,83 @@ def test_resid_few_rows_in_place_split_k():
     G.gemm_ref(G.NT, G.EPI_RESID, A.cpu(), B.cpu(), ref, bias=bias.cpu(), scale=scale.cpu(), res=x.cpu().clone(), alpha=1.0)
     G.gemm(G.NT, G.EPI_RESID, A, B, x, bias=bias, scale=scale, res=x, alpha=1.0)
     _check(x.cpu(), ref, tol=1e-3)
+
+
+# ---- production shapes: M = 32 x 1280 rows of the benchmark step, every epilogue (reference: the same PyTorch fp32
+# statement, evaluated on the GPU; TF32 stays off) -------------------------------------------------------------------
+M_PROD = 40960
+
+
+def _close(out, ref, tol):
+    err = (out.float() - ref.float()).abs().max().item()
+    den = ref.float().abs().max().item() + 1e-6
+    assert err / den < tol, f"rel err {err / den:.4g}"
+    # and not only where the magnitudes are large: mean error relative to mean magnitude
+    assert ((out.float() - ref.float()).abs().mean() / (ref.float().abs().mean() + 1e-9)).item() < tol
+
+
+@pytest.mark.parametrize("case", ["qkv_rotary", "outproj_resid_k1024", "ff2_resid_k4096", "ff1_geglu_pre", "ff2_dgrad_geglu_bwd",
+                                  "ff1_dgrad_nn", "ff1_wgrad_tn_colsum", "qkv_wgrad_tn", "head_logits"])
+def test_production_shapes(case):
+    assert not torch.backends.cuda.matmul.allow_tf32
+    M, D, Hd = M_PROD, 1024, 4096
+    dev = "cuda"
+    if case == "qkv_rotary":
+        seq = 1280
+        A, W = _rand(M, D), _rand(3 * D, D, scale=0.03)
+        ang = torch.rand(seq + 1, 32, device=dev) * 6.28
+        rot = torch.stack((ang.cos(), ang.sin()), dim=-1).contiguous()
+        out = torch.empty(M, 3 * D, device=dev, dtype=torch.bfloat16)
+        G.gemm(G.NT, G.EPI_ROTARY, A, W, out, rot=rot, seq_len=seq, q_cols=D, q_scale=0.125)
+        ref = torch.empty(M, 3 * D, device=dev)
+        G.gemm_ref(G.NT, G.EPI_ROTARY, A, W, ref, rot=rot, seq_len=seq, q_cols=D, q_scale=0.125)
+        _close(out, ref, 2e-2)
+    elif case in ("outproj_resid_k1024", "ff2_resid_k4096"):
+        K = 1024 if case == "outproj_resid_k1024" else Hd
+        A, W = _rand(M, K), _rand(D, K, scale=0.03)
+        bias, scale = torch.randn(D, device=dev), torch.rand(D, device=dev)
+        x0 = torch.randn(M, D, device=dev)
+        x, o2 = x0.clone(), torch.empty(M, D, device=dev, dtype=torch.bfloat16)
+        G.gemm(G.NT, G.EPI_RESID, A, W, x, out2=o2, bias=bias, scale=scale, res=x, alpha=1.0)
+        ref, ref2 = torch.empty(M, D, device=dev), torch.empty(M, D, device=dev)
+        G.gemm_ref(G.NT, G.EPI_RESID, A, W, ref, out2=ref2, bias=bias, scale=scale, res=x0, alpha=1.0)
+        _close(x, ref, 2e-3)
+        _close(o2, ref2, 2e-2)
+    elif case == "ff1_geglu_pre":
+        A, W = _rand(M, D), _rand(2 * Hd, D, scale=0.03)
+        bias = torch.randn(2 * Hd, device=dev) * 0.1
+        u, pre = torch.empty(M, Hd, device=dev, dtype=torch.bfloat16), torch.empty(M, 2 * Hd, device=dev, dtype=torch.bfloat16)
+        G.gemm(G.NT, G.EPI_GEGLU, A, W, u, out2=pre, bias=bias, n_half=Hd)
+        ref, refp = torch.empty(M, Hd, device=dev), torch.empty(M, 2 * Hd, device=dev)
+        G.gemm_ref(G.NT, G.EPI_GEGLU, A, W, ref, out2=refp, bias=bias, n_half=Hd)
+        _close(u, ref, 2e-2)
+        _close(pre, refp, 2e-2)
+    elif case == "ff2_dgrad_geglu_bwd":
+        dY, W2 = _rand(M, D), _rand(D, Hd, scale=0.05)
+        pre = _rand(M, 2 * Hd, scale=0.7)
+        dpre = torch.empty(M, 2 * Hd, device=dev, dtype=torch.bfloat16)
+        G.gemm(G.NN, G.EPI_GEGLU_BWD, dY, W2, dpre, aux=pre, n_half=Hd)
+        ref = torch.empty(M, 2 * Hd, device=dev)
+        G.gemm_ref(G.NN, G.EPI_GEGLU_BWD, dY, W2, ref, aux=pre, n_half=Hd)
+        _close(dpre, ref, 2e-2)
+    elif case == "ff1_dgrad_nn":
+        dpre, W1 = _rand(M, 2 * Hd), _rand(2 * Hd, D, scale=0.03)
+        dh = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
+        G.gemm(G.NN, G.EPI_BF16, dpre, W1, dh)
+        _close(dh, dpre.float() @ W1.float(), 2e-2)
+    elif case in ("ff1_wgrad_tn_colsum", "qkv_wgrad_tn"):
+        N_out = 2 * Hd if case == "ff1_wgrad_tn_colsum" else 3 * D
+        dY, h = _rand(M, N_out, scale=0.1), _rand(M, D, scale=0.1)
+        g0 = torch.randn(N_out, D, device=dev)
+        gW, cs = g0.clone(), torch.zeros(N_out, device=dev)
+        G.gemm(G.TN, G.EPI_ATOMIC_F32, dY, h, gW, a_colsum=cs if case == "ff1_wgrad_tn_colsum" else None)
+        _close(gW, g0 + dY.float().t() @ h.float(), 5e-3)
+        if case == "ff1_wgrad_tn_colsum":
+            _close(cs, dY.float().sum(0), 5e-3)
+    else:   # head_logits: one image-segment chunk of the tied vocabulary matrix
+        rows, nv = 8192, 8192
+        A, W = _rand(rows, D), _rand(nv, D, scale=0.03)
+        bias = torch.randn(nv, device=dev)
+        lg = torch.empty(rows, nv, device=dev, dtype=torch.bfloat16)
+        G.gemm(G.NT, G.EPI_BF16, A, W, lg, bias=bias)
+        _close(lg, A.float() @ W.float().t() + bias, 2e-2)

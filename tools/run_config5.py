@@ -26,7 +26,7 @@ groups = []
 for gi in range(2):
     devs = ",".join(str(gi * G + i) for i in range(G))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={G}", "--master-addr", "127.0.0.1",
-           "--master-port", str(29600 + gi), os.path.join(ROOT, "run_trainer_group.py"), *common, "--initial_peers", maddr,
+           "--master-port", str(29600 + gi), os.path.join(ROOT, "run_trainer.py"), *common, "--initial_peers", maddr,
            "--host_maddrs", "/ip4/127.0.0.1/tcp/0", "--per_device_train_batch_size", "4", "--max_steps", "24",
            "--seed", "0", "--learning_rate", "0.01", "--warmup_steps", "1"]
     groups.append(subprocess.Popen(cmd, stdout=open(os.path.join(work, f"group{gi}.log"), "w"), stderr=subprocess.STDOUT,
@@ -36,8 +36,13 @@ time.sleep(3)
 aux.terminate()
 logs = [open(os.path.join(work, f"group{gi}.log"), errors="ignore").read() for gi in range(2)]
 auxl = open(aux_log, errors="ignore").read()
-done = [re.search(r"GROUP_DONE epoch (\d+) param_checksum (\S+)", l) for l in logs]
+done = []
+for l in logs:   # run_trainer.py logs "GROUP_PARAM_CHECKSUM <sum> epoch <n>" on every rank at shutdown
+    m = re.findall(r"GROUP_PARAM_CHECKSUM (\S+) epoch (\d+)", l)
+    done.append(re.match(r"(\d+) (\S+)", f"{m[-1][1]} {m[-1][0]}") if m and len(set(m)) == 1 else None)
 print("rcs", rcs, "done", [d.groups() if d else None for d in done])
+rounds = [[float(t) for t in re.findall(r"swarm-averaged gradients, ([0-9.]+)s", l)] for l in logs]
+print("global-step times of swarm-averaged epochs (reduce inside the group + swarm round + group LAMB step), s:", rounds)
 print("swarm-averaged rounds:", [l.count("swarm-averaged") for l in logs], "group-local:", [l.count("group-local") for l in logs])
 print("aux epochs:", re.findall(r"Epoch #(\d+)", auxl)[-5:])
 ok = all(r == 0 for r in rcs) and all(done) and all(int(d.group(1)) >= 2 for d in done) and \
