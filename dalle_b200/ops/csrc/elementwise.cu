@@ -824,15 +824,17 @@ static int ln_shift_bwd_launch(const void* dh, const float* x, const float* x2, 
   const bool ring_ok = mode == 0 && !x2 && D % 64 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 &&
                        reinterpret_cast<uintptr_t>(dx) % 16 == 0 && reinterpret_cast<uintptr_t>(dh) % 16 == 0 &&
                        (!nx.o || reinterpret_cast<uintptr_t>(nx.o) % 16 == 0);
-  const int ring_rows = 2;
+  // rows in flight per 128-thread group (DALLE_B200_LNB_RING overrides: experiments)
+  static const int ring_env = [] { const char* e = getenv("DALLE_B200_LNB_RING"); return e ? atoi(e) : 0; }();
+  const int ring_rows = ring_env > 0 ? ring_env : 2;
   const size_t ring_smem = 2 * (static_cast<size_t>(ring_rows) * D * (nx.o ? 12 : 10) + ring_rows * 8);
   int blocks = num_sms() * 3;   // persistent: three 8-warp blocks per SM
   if (blocks * 2 > M) blocks = (M + 1) / 2;
-  if (ring_ok && ring_smem <= 80 * 1024) {
+  if (ring_ok && ring_smem <= 112 * 1024) {
     static bool configured = false;
     if (!configured) {
-      cudaFuncSetAttribute(ln_shift_bwd_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
-      cudaFuncSetAttribute(ln_shift_bwd_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024);
+      cudaFuncSetAttribute(ln_shift_bwd_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
+      cudaFuncSetAttribute(ln_shift_bwd_kernel<2, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024);
       configured = true;
     }
     if (nx.o && blocks > num_sms() * 2) blocks = num_sms() * 2;   // (register-limited to two blocks per SM)

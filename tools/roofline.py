@@ -147,9 +147,10 @@ def build_ops(B):
     add("out-proj wgrad (TN)", 1, gemm(G.TN, G.EPI_ATOMIC_F32, d_o, h, gWo), f(I, D), M * D * 2 * 2)
     add("QKV dgrad (NN)", 1, gemm(G.NN, G.EPI_BF16, dqkv2, Wq, dh), f(3 * I, D), M * 3 * I * 2 + M * D * 2)
     add("QKV wgrad (TN)", 1, gemm(G.TN, G.EPI_ATOMIC_F32, dqkv2, h, gWq), f(3 * I, D), M * 3 * I * 2 + M * D * 2)
-    add("LN + shift bwd", 2, lambda: E.ln_shift_bwd(h, x, None, mean, rstd, w, dx, None, dw, db, cfg, True, 0), 0.0,
-        M * D * 2 + M * D * 4 * 2 + M * D * 4)
-    add("residual bwd prep", 2, lambda: E.resid_bwd_prep(dy, ao, sc, dao, dsc, dbi), 0.0, M * D * 4 + M * D * 2 * 2)
+    o_n, d_on = rn(M, D).to(bf), torch.zeros(M, D, device=dev, dtype=bf)
+    add("LN + shift bwd + next block's residual prologue", 2,
+        lambda: E.ln_shift_bwd(h, x, None, mean, rstd, w, dx, None, dw, db, cfg, True, 0, next_prep=(o_n, sc, d_on, dsc, dbi)),
+        0.0, M * D * 2 + M * D * 4 * 2 + M * D * 4 + M * D * 2 * 2)
     add(f"head: logits GEMM ({rows_i} x {nv})", 0, gemm(G.NT, G.EPI_BF16, h[:rows_i], Wv, lg, bias=bv), 2.0 * rows_i * nv * D,
         rows_i * D * 2 + nv * D * 2 + rows_i * nv * 2)
     add(f"head: cross-entropy fwd+bwd ({rows_i} x {nv})", 0, lambda: E.ce_fwd_bwd(lg, labels, nv, 1e-4, gs, loss, write_grad=True),
