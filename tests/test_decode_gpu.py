@@ -245,3 +245,48 @@ def test_first_generation_engine_still_matches():
     ref = G.generate_codes_reference(model, text, top_k=1, use_cache=True, dtype=torch.float32)
     codes = DecodeEngineV1(model, 3).generate(text, temperature=1.0, top_k=1)
     assert torch.equal(codes[:, :32], ref[:, :32])
+
+
+def test_run_inference_on_the_gpu_goes_through_the_decode_engine(tmp_path):
+    """The public entry point (reference inference/run_inference.py:79-92) on CUDA: greedy codes written to the pickle
+    equal the PyTorch cached-decode oracle on the same checkpoint."""
+    import os
+    import pickle
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "inference"))
+    import run_inference
+    from dalle_b200.config import get_config
+    from dalle_b200.models.dalle import ModelWrapper
+    from dalle_b200.models import decode_engine
+
+    cfg = get_config("tiny")
+    model = DALLE(cfg, seed=0)
+    with torch.no_grad():
+        for p in list(model.scale_f) + list(model.scale_g):
+            p.fill_(0.3)
+        model.emb_weight.mul_(4.0)
+    ckpt = tmp_path / "model.pt"
+    torch.save(ModelWrapper(model).state_dict(), ckpt)
+    q = tmp_path / "queries.txt"
+    q.write_text("a cat\n")
+    out = tmp_path / "out"
+    made = []
+    orig = decode_engine.DecodeEngine.__init__
+    decode_engine.DecodeEngine.__init__ = lambda self, *a, **k: (made.append(1), orig(self, *a, **k))[1]
+    try:
+        run_inference.main(["--queries", str(q), "--temperature", "1.0", "--top-k", "1", "--model", str(ckpt),
+                            "--output-dir", str(out), "--model-preset", "tiny", "--batch-size", "2", "--n-iters", "1"])
+    finally:
+        decode_engine.DecodeEngine.__init__ = orig
+    assert made, "the CUDA path did not build a decode engine"
+    rec = pickle.load(open(out / "a cat.pickle", "rb"))
+    codes = torch.as_tensor(rec["codes"][0])
+    assert codes.shape == (cfg.image_seq_len,) and int(codes.min()) >= 0 and int(codes.max()) < cfg.num_image_tokens
+    # the oracle on the same prompt and weights
+    from dalle_b200.training.tokenizer import load_tokenizer
+
+    text = run_inference.encode_query("a cat", load_tokenizer("t5-small"), cfg.text_seq_len, 2, "cuda")
+    ref = G.generate_codes_reference(model.cuda(), text, top_k=1, use_cache=True, dtype=torch.float32)
+    assert torch.equal(codes[:32].cuda(), ref[0, :32]), (codes[:32], ref[0, :32])
