@@ -52,6 +52,9 @@ struct AttnBwd4Args {
   int n_text_chunks;           // q kernel: ceil(T_pad / 64) key chunks
   int n_text_tiles;            // kv kernel: 128-key text tiles (full ones, plus a partial one when it is not `tail`)
   int tail0, n_tail;           // leftover text keys [tail0, tail0 + n_tail) handled on CUDA cores (n_tail <= 4)
+  int text_shift;              // 1: text query blocks start at token 1; token 0 (sees itself only) is written directly
+  const __nv_bfloat16* qkv;
+  const __nv_bfloat16* d_out;
 };
 
 __device__ __forceinline__ void ab4_red_add_v2(float* p, float a, float b) {
@@ -128,7 +131,7 @@ __device__ __forceinline__ void attn_bwd4_q_body(const CUtensorMap& tmQ128, cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qw = warp & 3, ch = warp >> 2;      // TMEM lane quarter, column half
   const int h = blockIdx.y, b = blockIdx.z;
-  const int q0 = blk * 128;
+  const int q0 = blk * 128 + (MODE == ATT_TEXT ? a.text_shift : 0);
   const int HD = g.H * 64;
   const int row_base = b * g.seq;
   const int lines = 128 / g.F, lines64 = 64 / g.F;
@@ -369,6 +372,17 @@ __device__ __forceinline__ void attn_bwd4_q_body(const CUtensorMap& tmQ128, cons
     ab4_store_rows64(sK + warp * 2048, v, lane, q_valid ? row_base + tpos : -1, a.dqkv, 3 * HD, h * 64 + 32 * ch);
   }
 
+  if (MODE == ATT_TEXT && a.text_shift && blk == 0 && warp == 1) {
+    // token 0: P = 1 on its single key, so dS = dP - delta = 0: dq_0 = 0 and its dk_0 / dv_0 terms come out of the
+    // key/value kernel, which only needs delta_0 = dO_0 . o_0 = dO_0 . v_0.  Lane = two head dims.
+    const long long r0 = static_cast<long long>(row_base);
+    const float2 vf = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(a.qkv + r0 * 3 * HD + 2 * HD + h * 64 + 2 * lane));
+    const float2 df = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(a.d_out + r0 * HD + h * 64 + 2 * lane));
+    const float d0 = warp_sum(vf.x * df.x + vf.y * df.y);
+    *reinterpret_cast<uint32_t*>(a.dqkv + r0 * 3 * HD + h * 64 + 2 * lane) = 0u;
+    if (lane == 0) a.delta[(static_cast<long long>(b) * g.H + h) * g.seq] = d0;
+  }
+
   tc_fence_before();
   __syncthreads();
   if (warp == 0) {
@@ -414,7 +428,17 @@ attn_bwd4_kv_kernel(const __grid_constant__ CUtensorMap tmQ128, const __grid_con
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qw = warp & 3, ch = warp >> 2;
-  const int h = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, LONG CTAs FIRST: the text key tiles of every (sample, head) - each walks all ~20 query half-steps -
+  // take the lowest block indices, the two-step image tiles follow and level the tail of the grid.  (With tiles
+  // interleaved per (sample, head) the last wave ended on a few 20-step CTAs while most SMs idled.)
+  const int n_bh = g.B * g.H;
+  const int lin = blockIdx.x;
+  const bool text_tile = lin < a.n_text_tiles * n_bh;
+  const int lin2 = text_tile ? lin : lin - a.n_text_tiles * n_bh;
+  const int per_bh = text_tile ? a.n_text_tiles : g.n_img_blocks;
+  const int bh_lin = lin2 / per_bh;
+  const int tile = lin2 - bh_lin * per_bh;                                     // text tile index / image block index
+  const int b = bh_lin / g.H, h = bh_lin - b * g.H;
   const int HD = g.H * 64;
   const int row_base = b * g.seq;
   const int lines = 128 / g.F, lines64 = 64 / g.F;
@@ -422,8 +446,6 @@ attn_bwd4_kv_kernel(const __grid_constant__ CUtensorMap tmQ128, const __grid_con
   const int n_text_half = (g.T + 63) / 64;
 
   // key tile of this CTA and the query half-blocks (64 queries) that can see it
-  const bool text_tile = static_cast<int>(blockIdx.x) < a.n_text_tiles;
-  const int tile = text_tile ? blockIdx.x : blockIdx.x - a.n_text_tiles;   // text tile index / image block index
   const int tv0 = text_tile ? 2 * tile : 0;                               // first text half-step (causal)
   const int n_steps = text_tile ? n_img_half + (n_text_half - tv0) : 2;
   // step u -> (is_text_q, half-block index): text tiles take the image half-blocks first, then the text ones
@@ -683,13 +705,19 @@ static int launch_bwd4(const CUtensorMap* m, const AttnBwd4Args& a, cudaStream_t
     attr_done = true;
   }
   // m: 0 Q128, 1 Q64, 2 Qtail, 3 Qcol, 4 DO128, 5 DO64, 6 DOcol
+  // the text-query and image-query kernels touch disjoint query rows (their leftover-key partials meet through
+  // red.add): side by side on a forked stream; the key/value kernel needs delta from both and runs after the join
+  AttnFork* fk = attn_fork_state();
+  const cudaStream_t side = attn_fork(fk, st);
   dim3 gqt(a.g.n_text_blocks, a.g.H, a.g.B);
-  kqt<<<gqt, AB4_THREADS, AB4_SMEM, st>>>(m[0], m[1], m[2], m[3], m[4], m[6], a);
-  if (cudaGetLastError() != cudaSuccess) return -22;
+  kqt<<<gqt, AB4_THREADS, AB4_SMEM, side>>>(m[0], m[1], m[2], m[3], m[4], m[6], a);
+  const bool bad_t = cudaGetLastError() != cudaSuccess;
   dim3 gq(a.g.n_img_blocks, a.g.H, a.g.B);
   kq<<<gq, AB4_THREADS, AB4_SMEM, st>>>(m[0], m[1], m[2], m[3], m[4], m[6], a);
-  if (cudaGetLastError() != cudaSuccess) return -22;
-  dim3 gkv(a.n_text_tiles + a.g.n_img_blocks, a.g.H, a.g.B);
+  const bool bad_i = cudaGetLastError() != cudaSuccess;
+  attn_join(fk, side, st);
+  if (bad_t || bad_i) return -22;
+  dim3 gkv((a.n_text_tiles + a.g.n_img_blocks) * a.g.H * a.g.B);
   kkv<<<gkv, AB4_THREADS, AB4_SMEM, st>>>(m[0], m[1], m[3], m[5], m[6], a);
   if (cudaGetLastError() != cudaSuccess) return -22;
   if (a.n_tail > 0) {
@@ -717,6 +745,10 @@ int attn4_bwd(const void* qkv, const void* out, const void* d_out, const float* 
   a.rot = reinterpret_cast<const float2*>(rot);
   a.rot_t = reinterpret_cast<const float2*>(rot_t); a.rot_len = seq + 1; a.q_scale = q_scale;
   a.n_text_chunks = (g.T_pad + 63) / 64;
+  // same block shift as the forward (attn_fwd4_sm100.cu): T = 128 k + 1 -> query blocks start at token 1
+  a.text_shift = (T > 1 && T % 128 == 1) ? 1 : 0;
+  g.n_text_blocks = (T - a.text_shift + 127) / 128;
+  a.qkv = reinterpret_cast<const __nv_bfloat16*>(qkv); a.d_out = reinterpret_cast<const __nv_bfloat16*>(d_out);
   // text keys beyond the full 128-key tiles: a handful go to the CUDA-core path of the q kernel (they must then also
   // be the leading keys of its last 64-key chunk), more get a partial tile of their own
   const int rem = T % 128;

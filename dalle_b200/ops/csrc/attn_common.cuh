@@ -9,6 +9,7 @@
 //   CONV : 128 image queries (consecutive tokens) x (all text keys + tokens [q0-2F, q0+128))
 // q, k and v arrive already rotated (and q pre-scaled) from the QKV GEMM epilogue.
 #pragma once
+#include <cstdlib>
 #include "sm100_ptx.cuh"
 
 namespace b200 {
@@ -49,6 +50,44 @@ __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+
+// Host side: run two independent launches of one attention call CONCURRENTLY (the small text-block kernel beside the
+// image-block kernel): the caller's stream forks into a per-device side stream and joins it again, so stream order
+// towards earlier and later work is unchanged and the pattern is capturable in a CUDA graph.  The text kernels are
+// a few per cent of the work but took a quarter of the time when run alone (three partly filled waves); next to
+// the image kernel their CTAs fill its gaps.  DALLE_B200_ATTN_FORK=0 keeps the launches in one stream.
+struct AttnFork {
+  cudaStream_t side = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+  bool ok = false;
+};
+inline AttnFork* attn_fork_state() {
+  static thread_local AttnFork per_dev[64];
+  static const bool enabled = [] { const char* e = getenv("DALLE_B200_ATTN_FORK"); return !(e && e[0] == '0'); }();
+  if (!enabled) return nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  AttnFork& f = per_dev[dev];
+  if (!f.ok) {
+    if (cudaStreamCreateWithFlags(&f.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    f.ok = true;
+  }
+  return &f;
+}
+// side = stream for the forked launch (== st when forking is off); call attn_join(f, st) after both launches
+inline cudaStream_t attn_fork(AttnFork* f, cudaStream_t st) {
+  if (!f) return st;
+  if (cudaEventRecord(f->fork, st) != cudaSuccess || cudaStreamWaitEvent(f->side, f->fork, 0) != cudaSuccess) return st;
+  return f->side;
+}
+inline void attn_join(AttnFork* f, cudaStream_t side, cudaStream_t st) {
+  if (!f || side == st) return;
+  cudaEventRecord(f->join, side);
+  cudaStreamWaitEvent(st, f->join, 0);
 }
 
 }  // namespace b200

@@ -31,10 +31,12 @@ constexpr float AF4_RESCALE_LOG2 = 8.0f;
 
 struct AttnFwd4Args {
   AttnGeom g;
+  const void* qkv;
   __nv_bfloat16* out;
   float* lse;
   int ld_out;
   int n_text_chunks;   // ceil(T_pad / 64)
+  int text_shift;      // 1: the text query blocks start at token 1 (see attn4_fwd), token 0 is written directly
 };
 
 template <int IMG_MODE, bool TEXT>   // image pattern (ATT_ROW / ATT_COL); TEXT: this CTA is a text query block
@@ -59,7 +61,7 @@ __device__ __forceinline__ void attn_fwd4_body(const CUtensorMap& tm128, const C
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int h = blockIdx.y, b = blockIdx.z;
-  const int q0 = blk * 128;
+  const int q0 = blk * 128 + (MODE == ATT_TEXT ? a.text_shift : 0);
   const int HD = g.H * 64;
   const int row_base = b * g.seq;
   const int lines = 128 / g.F;          // grid lines per query block
@@ -360,6 +362,16 @@ __device__ __forceinline__ void attn_fwd4_body(const CUtensorMap& tm128, const C
     }
     if (q_valid) a.lse[(static_cast<long long>(b) * g.H + h) * g.seq + tpos] = m_used + log2f(l_run);
   }
+  if (MODE == ATT_TEXT && a.text_shift && blk == 0 && warp == 1) {
+    // token 0 attends to itself only: o = v_0, lse = (q_0 . k_0) log2(e).  Lane = two head dims.
+    const __nv_bfloat16* r0 = reinterpret_cast<const __nv_bfloat16*>(a.qkv) + static_cast<long long>(row_base) * 3 * HD + h * 64 + 2 * lane;
+    const float2 qf = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(r0));
+    const float2 kf = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(r0 + HD));
+    const float s = warp_sum(qf.x * kf.x + qf.y * kf.y);
+    *reinterpret_cast<uint32_t*>(a.out + static_cast<long long>(row_base) * a.ld_out + h * 64 + 2 * lane) =
+        *reinterpret_cast<const uint32_t*>(r0 + 2 * HD);
+    if (lane == 0) a.lse[(static_cast<long long>(b) * g.H + h) * g.seq] = s * kLog2e;
+  }
 
   tc_fence_before();
   __syncthreads();
@@ -403,8 +415,13 @@ int attn4_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int
   g.B = B; g.H = H; g.seq = seq; g.T = T; g.T_pad = (T + 15) / 16 * 16; g.F = F; g.P = F * F;
   g.n_text_blocks = (T + 127) / 128; g.n_img_blocks = g.P / 128; g.conv_half = 0;
   if (g.P % 128 || 32 % F || seq != T + g.P - 1) return 1;
-  a.out = reinterpret_cast<__nv_bfloat16*>(out); a.lse = lse; a.ld_out = H * 64;
+  a.out = reinterpret_cast<__nv_bfloat16*>(out); a.lse = lse; a.ld_out = H * 64; a.qkv = qkv;
   a.n_text_chunks = (g.T_pad + 63) / 64;
+  // T = 128 k + 1 (257 here): with blocks starting at token 0 the last block would hold ONE query and still walk every
+  // key chunk.  Token 0 sees only itself, so it is written directly and the blocks start at token 1: 3 + 5 instead of
+  // 2 + 4 + 5 chunk passes per (sample, head).
+  a.text_shift = (T > 1 && T % 128 == 1) ? 1 : 0;
+  g.n_text_blocks = (T - a.text_shift + 127) / 128;
   CUtensorMap t128, t64, ttail, tunused, tcol;
   int rc = attn_make_maps(qkv, g, ATT_COL, &t128, &tunused, &tcol);
   if (rc) return rc;
@@ -414,10 +431,14 @@ int attn4_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int
   const int tail = g.T_pad % 64;
   rc = make_tmap_bf16_2d(&ttail, qkv, rows, cols, cols, 64, tail ? tail : 64);
   if (rc) return rc;
-  rc = launch_fwd4<ATT_ROW, true>(t128, t64, ttail, tcol, a, st);
-  if (rc) return rc;
-  return mode == ATT_ROW ? launch_fwd4<ATT_ROW, false>(t128, t64, ttail, tcol, a, st)
-                         : launch_fwd4<ATT_COL, false>(t128, t64, ttail, tcol, a, st);
+  // text blocks and image blocks write disjoint rows: the two launches run side by side (attn_common.cuh)
+  AttnFork* fk = attn_fork_state();
+  const cudaStream_t side = attn_fork(fk, st);
+  rc = launch_fwd4<ATT_ROW, true>(t128, t64, ttail, tcol, a, side);
+  const int rc2 = mode == ATT_ROW ? launch_fwd4<ATT_ROW, false>(t128, t64, ttail, tcol, a, st)
+                                  : launch_fwd4<ATT_COL, false>(t128, t64, ttail, tcol, a, st);
+  attn_join(fk, side, st);
+  return rc ? rc : rc2;
 }
 
 }  // namespace b200
