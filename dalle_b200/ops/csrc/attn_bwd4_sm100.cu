@@ -707,7 +707,7 @@ static int launch_bwd4(const CUtensorMap* m, const AttnBwd4Args& a, cudaStream_t
   // m: 0 Q128, 1 Q64, 2 Qtail, 3 Qcol, 4 DO128, 5 DO64, 6 DOcol
   // the text-query and image-query kernels touch disjoint query rows (their leftover-key partials meet through
   // red.add): side by side on a forked stream; the key/value kernel needs delta from both and runs after the join
-  AttnFork* fk = attn_fork_state();
+  AttnFork* fk = attn_fork_state(3);
   const cudaStream_t side = attn_fork(fk, st);
   dim3 gqt(a.g.n_text_blocks, a.g.H, a.g.B);
   kqt<<<gqt, AB4_THREADS, AB4_SMEM, side>>>(m[0], m[1], m[2], m[3], m[4], m[6], a);

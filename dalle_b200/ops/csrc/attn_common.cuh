@@ -57,16 +57,20 @@ __device__ __forceinline__ float fast_exp2(float x) {
 // image-block kernel): the caller's stream forks into a per-device side stream and joins it again, so stream order
 // towards earlier and later work is unchanged and the pattern is capturable in a CUDA graph.  The text kernels are
 // a few per cent of the work but took a quarter of the time when run alone (three partly filled waves); next to
-// the image kernel their CTAs fill its gaps.  DALLE_B200_ATTN_FORK=0 keeps the launches in one stream.
+// the image kernel their CTAs fill its gaps (-8 us forward, -11 us backward per layer).
+// DALLE_B200_ATTN_FORK=0 keeps the launches in one stream (2 = fork the forward only, 3 = the backward only).
+// (Run-to-run differences of ~1e-3 in some gradients seen while this was introduced were traced to the
+// convolution-like layer's backward, whose shared-key gradients meet through fp32 red.add before the bf16 store: the
+// order of the atomics flips single bf16 ulps, with or without the fork - tools/exp/flake_attn_bwd.py.)
 struct AttnFork {
   cudaStream_t side = nullptr;
   cudaEvent_t fork = nullptr, join = nullptr;
   bool ok = false;
 };
-inline AttnFork* attn_fork_state() {
+inline AttnFork* attn_fork_state(int which = 1) {   // which: 2 forward, 3 backward (DALLE_B200_ATTN_FORK=2|3 selects one)
   static thread_local AttnFork per_dev[64];
-  static const bool enabled = [] { const char* e = getenv("DALLE_B200_ATTN_FORK"); return !(e && e[0] == '0'); }();
-  if (!enabled) return nullptr;
+  static const int mode = [] { const char* e = getenv("DALLE_B200_ATTN_FORK"); return e ? atoi(e) : 1; }();
+  if (mode == 0 || (mode > 1 && mode != which)) return nullptr;
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
   AttnFork& f = per_dev[dev];
@@ -88,6 +92,7 @@ inline void attn_join(AttnFork* f, cudaStream_t side, cudaStream_t st) {
   if (!f || side == st) return;
   cudaEventRecord(f->join, side);
   cudaStreamWaitEvent(st, f->join, 0);
+
 }
 
 }  // namespace b200

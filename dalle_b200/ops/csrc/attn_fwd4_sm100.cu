@@ -432,7 +432,7 @@ int attn4_fwd(const void* qkv, void* out, float* lse, int B, int H, int seq, int
   rc = make_tmap_bf16_2d(&ttail, qkv, rows, cols, cols, 64, tail ? tail : 64);
   if (rc) return rc;
   // text blocks and image blocks write disjoint rows: the two launches run side by side (attn_common.cuh)
-  AttnFork* fk = attn_fork_state();
+  AttnFork* fk = attn_fork_state(2);
   const cudaStream_t side = attn_fork(fk, st);
   rc = launch_fwd4<ATT_ROW, true>(t128, t64, ttail, tcol, a, side);
   const int rc2 = mode == ATT_ROW ? launch_fwd4<ATT_ROW, false>(t128, t64, ttail, tcol, a, st)

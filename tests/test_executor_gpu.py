@@ -143,6 +143,13 @@ def test_head_gradient_in_the_forward_pass_gives_the_same_gradients():
         torch.cuda.synchronize()
         grads[mode] = (loss.item(), {n: p.grad.clone() for n, p in model.named_parameters()})
     assert abs(grads["two-pass"][0] - grads["fused"][0]) < 1e-5
+    # Two identical steps are not bit-identical: the convolution-like layer's backward sums shared-key gradients with
+    # fp32 red.add before the bf16 store, and the order of the atomics flips single bf16 ulps (2^-8) that travel down
+    # the stack (tools/exp/flake_attn_bwd.py).  Hence a bound of a few ulps on the maximum and a cosine on the whole.
     for n, g in grads["two-pass"][1].items():
-        d = (g - grads["fused"][1][n]).abs().max().item()
-        assert d <= 2e-3 * (g.abs().max().item() + 1e-8), (n, d)
+        f = grads["fused"][1][n]
+        d = (g - f).abs().max().item()
+        assert d <= 2e-2 * (g.abs().max().item() + 1e-8), (n, d)
+        if g.numel() > 8 and g.abs().max().item() > 0:
+            cos = torch.nn.functional.cosine_similarity(g.flatten().double(), f.flatten().double(), dim=0).item()
+            assert cos > 0.99999, (n, cos)
