@@ -294,8 +294,11 @@ class DecodeEngine:
         self.x2[:B].copy_(b.x2.view(B, n, cfg.dim)[:, T - 1])
 
     @torch.no_grad()
-    def generate(self, text: torch.Tensor, *, temperature=1.0, top_k=0, top_p=1.0, generator=None,
-                 use_graph: bool = True, prefill: bool = True) -> torch.Tensor:
+    def begin(self, text: torch.Tensor, *, temperature=1.0, top_k=0, top_p=1.0, generator=None, use_graph: bool = True,
+              prefill: bool = True) -> int:
+        """First half of ``generate``: prompt pass and first image code; returns the first position still to decode.
+        ``step_once`` then advances one position per call and ``result`` returns the codes - split so that several
+        engines (streams) can be interleaved by one host loop (``generate_many``)."""
         cfg = self.cfg
         assert text.shape[0] == self.batch
         text = text[:, : cfg.text_seq_len]
@@ -303,9 +306,11 @@ class DecodeEngine:
         text = torch.where(text == 0, pad_ids, text)
         seed = int(generator.initial_seed()) if generator is not None else int(torch.seed() & 0x7FFFFFFFFFFFFFFF)
         T = cfg.text_len
+        self._sampling = (temperature, top_k, top_p)
+        self._g_step = self._g_head = None
         if use_graph:
-            g_step = self._graph("step", temperature, top_k, top_p)
-            g_head = self._graph("head", temperature, top_k, top_p)
+            self._g_step = self._graph("step", temperature, top_k, top_p)
+            self._g_head = self._graph("head", temperature, top_k, top_p)
         # (graph construction ran warm-up steps: reset the state afterwards)
         self.ids.zero_()
         self.ids[:, 1:T] = text
@@ -315,19 +320,56 @@ class DecodeEngine:
             self._prefill(text)
             self.pos.fill_(T - 1)
             if use_graph:
-                g_head.replay()              # first image code from the prompt's last position
+                self._g_head.replay()        # first image code from the prompt's last position
             else:
                 self._head(temperature, top_k, top_p)
-            first = T
+            return T
+        # position-by-position prompt (kept for tests: must give the same codes as the batched prefill)
+        self.pos.zero_()
+        for pos in range(T - 1):
+            self._step(False, temperature, top_k, top_p)
+        return T - 1
+
+    def step_once(self):
+        if self._g_step is not None:
+            self._g_step.replay()
         else:
-            # position-by-position prompt (kept for tests: must give the same codes as the batched prefill)
-            self.pos.zero_()
-            for pos in range(T - 1):
-                self._step(False, temperature, top_k, top_p)
-            first = T - 1
-        for pos in range(first, cfg.seq_len):
-            if use_graph:
-                g_step.replay()
-            else:
-                self._step(True, temperature, top_k, top_p)
+            self._step(True, *self._sampling)
+
+    def result(self) -> torch.Tensor:
         return self.codes.clone()
+
+    @torch.no_grad()
+    def generate(self, text: torch.Tensor, *, temperature=1.0, top_k=0, top_p=1.0, generator=None,
+                 use_graph: bool = True, prefill: bool = True) -> torch.Tensor:
+        first = self.begin(text, temperature=temperature, top_k=top_k, top_p=top_p, generator=generator,
+                           use_graph=use_graph, prefill=prefill)
+        for pos in range(first, self.cfg.seq_len):
+            self.step_once()
+        return self.result()
+
+
+@torch.no_grad()
+def generate_many(engines, texts, *, temperature=1.0, top_k=0, top_p=1.0, generator=None):
+    """Several batches decoded CONCURRENTLY on one GPU: one engine and one CUDA stream per batch, graph replays
+    interleaved position by position.  A batch-32 decode step is a latency chain that leaves most SMs idle most of the
+    time; a second (third) chain fills them, so the GPU's tokens/s grows while a request's latency barely moves."""
+    streams = [torch.cuda.Stream() for _ in engines]
+    cur = torch.cuda.current_stream()
+    firsts = []
+    for eng, text in zip(engines, texts):        # prompt passes use the shared training-forward buffers: one at a time
+        if not hasattr(eng, "begin"):   # a first-generation engine (configuration outside decode2.cu): no interleaving
+            return [e.generate(t, temperature=temperature, top_k=top_k, top_p=top_p, generator=generator)
+                    for e, t in zip(engines, texts)]
+        firsts.append(eng.begin(text, temperature=temperature, top_k=top_k, top_p=top_p, generator=generator))
+    assert len(set(firsts)) == 1
+    for s in streams:
+        s.wait_stream(cur)
+    n = engines[0].cfg.seq_len
+    for pos in range(firsts[0], n):
+        for eng, s in zip(engines, streams):
+            with torch.cuda.stream(s):
+                eng.step_once()
+    for s in streams:
+        cur.wait_stream(s)
+    return [eng.result() for eng in engines]

@@ -166,12 +166,23 @@ def generate_images(model, text, *, temperature=1.0, top_k=0, top_p=1.0, use_cac
     codes = None
     if text.is_cuda and use_cache and model.cfg.dim_head == 64:
         try:
-            from .decode_engine import DecodeEngine
+            from .decode_engine import DecodeEngine, generate_many
 
-            eng = getattr(model, "_decode_engine", None)
-            if eng is None or eng.batch != text.shape[0]:
-                eng = model._decode_engine = DecodeEngine(model, text.shape[0])
-            codes = eng.generate(text, temperature=temperature, top_k=top_k, top_p=top_p, generator=generator)
+            B = text.shape[0]
+            if B <= DecodeEngine.MAX_BATCH:
+                eng = getattr(model, "_decode_engine", None)
+                if eng is None or eng.batch != B:
+                    eng = model._decode_engine = DecodeEngine(model, B)
+                codes = eng.generate(text, temperature=temperature, top_k=top_k, top_p=top_p, generator=generator)
+            else:
+                # larger batches: slices of <= 32 prompts, one engine and one stream each, decoded concurrently
+                sizes = [min(DecodeEngine.MAX_BATCH, B - o) for o in range(0, B, DecodeEngine.MAX_BATCH)]
+                engs = getattr(model, "_decode_engines", None)
+                if engs is None or [e.batch for e in engs] != sizes:
+                    engs = model._decode_engines = [DecodeEngine(model, n) for n in sizes]
+                parts = generate_many(engs, list(text.split(DecodeEngine.MAX_BATCH)), temperature=temperature,
+                                      top_k=top_k, top_p=top_p, generator=generator)
+                codes = torch.cat(parts, dim=0)
         except ImportError:
             codes = None
     if codes is None:

@@ -290,3 +290,22 @@ def test_run_inference_on_the_gpu_goes_through_the_decode_engine(tmp_path):
     text = run_inference.encode_query("a cat", load_tokenizer("t5-small"), cfg.text_seq_len, 2, "cuda")
     ref = G.generate_codes_reference(model.cuda(), text, top_k=1, use_cache=True, dtype=torch.float32)
     assert torch.equal(codes[:32].cuda(), ref[0, :32]), (codes[:32], ref[0, :32])
+
+
+def test_batches_above_32_run_as_concurrent_engines():
+    """generate_images with 40 prompts: slices of 32 + 8 on two engines / streams, interleaved position by position;
+    greedy codes of every prompt equal the oracle's (the slices must not disturb each other's caches or position)."""
+    cfg = _cfg()
+    torch.manual_seed(0)
+    model = DALLE(cfg, seed=0)
+    with torch.no_grad():
+        for p in list(model.scale_f) + list(model.scale_g):
+            p.fill_(0.3)
+        model.emb_weight.mul_(4.0)
+    model.cuda()
+    text = torch.randint(1, cfg.num_text_tokens, (40, cfg.text_seq_len), device="cuda")
+    codes = G.generate_images(model, text, top_k=1, return_codes=True)
+    assert codes.shape == (40, cfg.image_seq_len) and len(model._decode_engines) == 2
+    ref = G.generate_codes_reference(model, text, top_k=1, use_cache=True, dtype=torch.float32)
+    assert torch.equal(codes[:, :24], ref[:, :24]), (codes[:, :24] != ref[:, :24]).nonzero()[:5]
+    assert (codes == ref).float().mean().item() > 0.5
