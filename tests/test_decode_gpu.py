@@ -309,3 +309,35 @@ def test_batches_above_32_run_as_concurrent_engines():
     ref = G.generate_codes_reference(model, text, top_k=1, use_cache=True, dtype=torch.float32)
     assert torch.equal(codes[:, :24], ref[:, :24]), (codes[:, :24] != ref[:, :24]).nonzero()[:5]
     assert (codes == ref).float().mean().item() > 0.5
+
+
+def test_run_inference_iterations_share_one_concurrent_call(tmp_path):
+    """--batch-size 20 --n-iters 2 on CUDA: the 40 prompts go through one generate_images call (two concurrent
+    engines); greedy sampling of the same query must give the same codes in every row of both iterations."""
+    import os
+    import pickle
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "inference"))
+    import run_inference
+    from dalle_b200.config import get_config
+    from dalle_b200.models.dalle import ModelWrapper
+
+    cfg = get_config("tiny")
+    model = DALLE(cfg, seed=0)
+    with torch.no_grad():
+        for p in list(model.scale_f) + list(model.scale_g):
+            p.fill_(0.3)
+        model.emb_weight.mul_(4.0)
+    ckpt = tmp_path / "model.pt"
+    torch.save(ModelWrapper(model).state_dict(), ckpt)
+    q = tmp_path / "queries.txt"
+    q.write_text("a dog\n")
+    out = tmp_path / "out"
+    run_inference.main(["--queries", str(q), "--temperature", "1.0", "--top-k", "1", "--model", str(ckpt),
+                        "--output-dir", str(out), "--model-preset", "tiny", "--batch-size", "20", "--n-iters", "2"])
+    rec = pickle.load(open(out / "a dog.pickle", "rb"))
+    codes = torch.as_tensor(__import__("numpy").stack(rec["codes"]))
+    assert codes.shape == (40, cfg.image_seq_len)
+    assert (codes[:, :32] == codes[0, :32]).all(), "rows of one greedy query differ"
