@@ -146,9 +146,9 @@ class DecodeEngineV1:
 
 class DecodeEngine:
     """See the module docstring.  ``DecodeEngine(model, batch)`` returns a first-generation engine when the
-    configuration is outside what decode2.cu tiles (batch > 32, dense-causal layers, long local windows)."""
+    configuration is outside what decode2.cu tiles (batch > 64, dense-causal layers, long local windows)."""
 
-    MAX_BATCH = 32
+    MAX_BATCH = 64
 
     def __new__(cls, model, batch: int):
         cfg = model.cfg
@@ -162,7 +162,8 @@ class DecodeEngine:
         assert cfg.dim_head == 64 and cfg.conv_dilation == 1
         self.model, self.cfg, self.batch = model, cfg, batch
         dev = model.emb_weight.device
-        R, D, I, n = self.MAX_BATCH, cfg.dim, cfg.inner_dim, cfg.seq_len      # every activation buffer has 32 rows
+        R = self.rows = 32 if batch <= 32 else 64     # batch tile of the skinny GEMMs: every activation buffer has R rows
+        D, I, n = cfg.dim, cfg.inner_dim, cfg.seq_len
         hid = D * cfg.ff_mult
         bf = torch.bfloat16
         z = lambda *s, dtype=bf: torch.zeros(*s, device=dev, dtype=dtype)
@@ -201,7 +202,7 @@ class DecodeEngine:
             None if ln is None else ln[0].data_ptr(), None if ln is None else ln[1].data_ptr(), ptr(ring),
             self.pos.data_ptr(), cfg.text_len, cfg.image_fmap_size, cfg.ln_eps, ptr(bias), ptr(scale), ptr(xout),
             None if site_out is None else self.stats[site_out].data_ptr(), ptr(out), ldo, ptr(rot), q_cols, q_scale,
-            torch.cuda.current_stream().cuda_stream), "decode2_gemm")
+            self.rows, torch.cuda.current_stream().cuda_stream), "decode2_gemm")
 
     def _layers(self):
         m, cfg, L = self.model, self.cfg, lib.cuda_lib()
@@ -228,7 +229,7 @@ class DecodeEngine:
         st = torch.cuda.current_stream().cuda_stream
         pp = self.pos.data_ptr()
         lib.check(L.b200_decode_ln_shift(self.x1.data_ptr(), self.x2.data_ptr(), m.final_norm_w.data_ptr(),
-                                         m.final_norm_b.data_ptr(), None, self.hf.data_ptr(), pp, self.MAX_BATCH, cfg.dim,
+                                         m.final_norm_b.data_ptr(), None, self.hf.data_ptr(), pp, self.rows, cfg.dim,
                                          cfg.seq_len, cfg.text_len, cfg.image_fmap_size, cfg.ln_eps, 0, st),
                   "decode_final_norm")
         v0, nv = cfg.total_text_tokens, cfg.num_image_tokens
@@ -245,7 +246,7 @@ class DecodeEngine:
         st = torch.cuda.current_stream().cuda_stream
         lib.check(L.b200_decode2_embed(self.ids.data_ptr(), self.ids.shape[1], m.emb_weight.data_ptr(),
                                        self.x1.data_ptr(), self.x2.data_ptr(), self.stats.data_ptr(), self.n_sites,
-                                       self.pos.data_ptr(), self.batch, cfg.dim, st), "decode2_embed")
+                                       self.pos.data_ptr(), self.batch, cfg.dim, self.rows, st), "decode2_embed")
         self._layers()
         if with_head:
             self._head(temperature, top_k, top_p)

@@ -32,7 +32,7 @@ namespace b200 {
 int make_tmap_bf16_2d(CUtensorMap* m, const void* ptr, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_cols,
                       uint32_t box_rows);
 
-constexpr int DG_NB = 32;          // batch tile = MMA N
+constexpr int DG_NB_MAX = 64;      // batch tile = MMA N: 32 or 64 rows (template parameter NB)
 constexpr int DG_THREADS = 128;
 constexpr int DG_PART_LD = 132;    // floats per batch row of the partial tile (16-byte aligned, conflict-free writes)
 constexpr int DG_MAX_KB = 8;       // K slice <= 512
@@ -73,14 +73,14 @@ __device__ __forceinline__ float4 ld_cluster_f4(uint32_t addr) {
   return v;
 }
 
-template <int EPI, int PRO>
+template <int EPI, int PRO, int NB>
 __global__ void __launch_bounds__(DG_THREADS)
 dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const DecGemmArgs a) {
   extern __shared__ uint8_t dg_smem_raw[];
   __shared__ __align__(8) uint64_t bar_k[DG_MAX_KB];
   __shared__ __align__(8) uint64_t bar_mma;
   __shared__ uint32_t tmem_slot;
-  __shared__ float s_mean[DG_NB], s_rstd[DG_NB];
+  __shared__ float s_mean[NB], s_rstd[NB];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dg_smem_raw) + 1023) & ~uintptr_t(1023));
   const int tid = threadIdx.x, warp = tid >> 5;
   const int nkb = a.ks >> 6;
@@ -88,8 +88,9 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   const int mt = blockIdx.x / a.ksplit;
   const int k0 = static_cast<int>(ksr) * a.ks;
   uint8_t* sW = smem;                                  // nkb tiles of 128 rows x 128 bytes
-  uint8_t* sX = smem + nkb * 16384;                    // nkb tiles of 32 rows x 128 bytes
-  float* part = reinterpret_cast<float*>(sX + nkb * 4096);   // [32][DG_PART_LD]
+  constexpr int XT = NB * 128;                         // bytes of one B tile (NB rows x 64 bf16)
+  uint8_t* sX = smem + nkb * 16384;                    // nkb tiles of NB rows x 128 bytes
+  float* part = reinterpret_cast<float*>(sX + nkb * XT);     // [NB][DG_PART_LD]
 
   if (warp == 0 && elect_one()) {
     for (int kb = 0; kb < nkb; ++kb) mbar_init(&bar_k[kb], 1);
@@ -97,7 +98,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     fence_barrier_init();
     // weights depend on nothing that runs before this kernel: the whole K slice goes in flight now
     for (int kb = 0; kb < nkb; ++kb) {
-      mbar_expect_tx(&bar_k[kb], 16384 + (PRO == DP_TMA ? 4096 : 0));
+      mbar_expect_tx(&bar_k[kb], 16384 + (PRO == DP_TMA ? XT : 0));
       if (EPI == DG_GEGLU) {   // 64 value rows + the 64 gate rows of the same features
         tma_load_2d(sW + kb * 16384, &tmW, &bar_k[kb], k0 + kb * 64, mt * 64);
         tma_load_2d(sW + kb * 16384 + 8192, &tmW, &bar_k[kb], k0 + kb * 64, a.N + mt * 64);
@@ -107,21 +108,21 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
   }
   if (warp == 1) {
-    tmem_alloc(&tmem_slot, 32);
+    tmem_alloc(&tmem_slot, NB);
     tmem_relinquish();
   }
   griddep_launch();
   griddep_wait();            // everything below may read what the previous kernels wrote
   if (PRO == DP_TMA) {
     if (warp == 0 && elect_one())
-      for (int kb = 0; kb < nkb; ++kb) tma_load_2d(sX + kb * 4096, &tmX, &bar_k[kb], k0 + kb * 64, 0);
+      for (int kb = 0; kb < nkb; ++kb) tma_load_2d(sX + kb * XT, &tmX, &bar_k[kb], k0 + kb * 64, 0);
   } else {
     // ---- layer norm + token shift of this CTA's K slice, written as the 128B-swizzled B tile ----
     // thread <-> one 16-byte chunk (8 channels) of the slice and every (128 / chunks)-th row: the norm weights are
     // loaded once per thread, a warp reads whole contiguous pieces of a row, and the loads of eight rows are in
     // flight together (the kernel is a latency chain: the first version walked 8 dependent round trips here).
     const int pos = __ldg(a.pos_ptr);
-    if (tid < 32) {
+    if (tid < NB) {
       const float invK = 1.0f / a.K;
       const float2 st = *reinterpret_cast<const float2*>(a.stats_in + tid * 2);
       const float mean = st.x * invK;
@@ -139,7 +140,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     const int halfK = a.K >> 1, quartK = a.K >> 2;
     const int nch = a.ks >> 3;                       // chunks per row of the slice: 8 .. 64
     const int ch = tid % nch, r0 = tid / nch;
-    const int rstep = DG_THREADS / nch, nrows = DG_NB / rstep;
+    const int rstep = DG_THREADS / nch, nrows = NB / rstep;
     const int gc = k0 + ch * 8;
     const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.ln_w + gc));
     const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.ln_w + gc + 4));
@@ -177,7 +178,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
               *reinterpret_cast<uint4*>(a.ring + (static_cast<long long>(r) * 64 + (pos & 63)) * halfK + gc) = o;
             o = rg[u];
           }
-          *reinterpret_cast<uint4*>(sX + (ch >> 3) * 4096 + r * 128 + (((ch & 7) ^ (r & 7)) << 4)) = o;
+          *reinterpret_cast<uint4*>(sX + (ch >> 3) * XT + r * 128 + (((ch & 7) ^ (r & 7)) << 4)) = o;
         }
       }
     }
@@ -188,11 +189,11 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   const uint32_t tmem = tmem_slot;
 
   if (warp == 0 && elect_one()) {
-    constexpr uint32_t idesc = make_idesc_bf16(128, DG_NB, 0, 0);
+    constexpr uint32_t idesc = make_idesc_bf16(128, NB, 0, 0);
     for (int kb = 0; kb < nkb; ++kb) {
       mbar_wait(&bar_k[kb], 0);
       tc_fence_after();
-      const uint32_t wa = smem_u32(sW + kb * 16384), xa = smem_u32(sX + kb * 4096);
+      const uint32_t wa = smem_u32(sW + kb * 16384), xa = smem_u32(sX + kb * XT);
 #pragma unroll
       for (int k16 = 0; k16 < 4; ++k16)
         umma_bf16_ss(tmem, make_smem_desc_sw128(wa + k16 * 32, 16, 1024), make_smem_desc_sw128(xa + k16 * 32, 16, 1024),
@@ -202,7 +203,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   }
   // epilogue operands of this thread's first (usually only) group of features: requested now, so that their L2
   // round trip runs under the MMAs and the cluster exchange instead of after them
-  const int b = tid >> 2, fq = tid & 3;
+  const int b0 = tid >> 2, fq = tid & 3;
   const int own = (EPI == DG_GEGLU ? 64 : 128) / a.ksplit;
   const int n_first = mt * (EPI == DG_GEGLU ? 64 : 128) + static_cast<int>(ksr) * own + 4 * fq;
   float4 pre0 = make_float4(0.f, 0.f, 0.f, 0.f), pre1 = pre0, pre2 = pre0;
@@ -213,7 +214,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     } else if (EPI == DG_RESID) {
       pre0 = __ldg(reinterpret_cast<const float4*>(a.bias + n_first));
       pre1 = __ldg(reinterpret_cast<const float4*>(a.scale + n_first));
-      pre2 = *reinterpret_cast<const float4*>(a.xout + static_cast<long long>(b) * a.N + n_first);
+      pre2 = *reinterpret_cast<const float4*>(a.xout + static_cast<long long>(b0) * a.N + n_first);
     } else if (EPI == DG_QKV) {
       const float2* rt = a.rot + static_cast<long long>(__ldg(a.pos_ptr)) * 32 + ((n_first & 63) >> 1);
       const float2 c0 = __ldg(rt), c1 = __ldg(rt + 1);
@@ -224,16 +225,22 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   mbar_wait(&bar_mma, 0);
   tc_fence_after();
   {
-    uint32_t v[32];
-    tmem_ld32(tmem + (static_cast<uint32_t>(warp * 32) << 16), v);
-    tmem_ld_wait();
 #pragma unroll
-    for (int j = 0; j < 32; ++j) part[j * DG_PART_LD + tid] = __uint_as_float(v[j]);   // part[batch][feature]
+    for (int jb = 0; jb < NB; jb += 32) {
+      uint32_t v[32];
+      tmem_ld32(tmem + (static_cast<uint32_t>(warp * 32) << 16) + jb, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) part[(jb + j) * DG_PART_LD + tid] = __uint_as_float(v[j]);   // part[batch][feature]
+    }
   }
   tc_fence_before();
   cluster_sync_all();        // every CTA's partial tile is in its shared memory
 
   // ---- reduce over the K splits and finish: this CTA owns 128 / ksplit of the tile's features ----
+#pragma unroll 1
+  for (int bb = 0; bb < NB; bb += 32) {
+  const int b = bb + b0;
   if (EPI == DG_GEGLU) {
     const int nj = 64 / a.ksplit;
     for (int g = 0; g < nj / 16; ++g) {
@@ -284,7 +291,7 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         const float4 bi = g == 0 ? pre0 : __ldg(reinterpret_cast<const float4*>(a.bias + n));
         const float4 sc = g == 0 ? pre1 : __ldg(reinterpret_cast<const float4*>(a.scale + n));
         float4* xp = reinterpret_cast<float4*>(a.xout + static_cast<long long>(b) * a.N + n);
-        float4 xo = g == 0 ? pre2 : *xp;
+        float4 xo = (g == 0 && bb == 0) ? pre2 : *xp;
         xo.x += sc.x * (acc.x + bi.x); xo.y += sc.y * (acc.y + bi.y);
         xo.z += sc.z * (acc.z + bi.z); xo.w += sc.w * (acc.w + bi.w);
         *xp = xo;
@@ -307,8 +314,9 @@ dec_gemm_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       }
     }
   }
+  }   // batch groups of 32 rows
   cluster_sync_all();        // nobody leaves while a neighbour still reads its partial tile
-  if (warp == 1) tmem_dealloc(tmem, 32);
+  if (warp == 1) tmem_dealloc(tmem, NB);
 }
 
 
@@ -500,24 +508,24 @@ dec_attn2_kernel(const DecAttnArgs a) {
 __global__ void __launch_bounds__(1024)
 dec_embed2_kernel(const long long* __restrict__ ids, int ids_stride, const float* __restrict__ W, float* __restrict__ x1,
                   float* __restrict__ x2, float* __restrict__ stats, int n_sites, const int* __restrict__ pos_ptr, int B,
-                  int D) {
-  const int b = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = 64 + threadIdx.x; i < n_sites * 64; i += 1024) stats[i] = 0.f;
-  float s0 = 0.f, s1 = 0.f;
-  {
+                  int D, int NB) {
+  const int lane = threadIdx.x & 31;
+  for (int i = NB * 2 + threadIdx.x; i < n_sites * NB * 2; i += 1024) stats[i] = 0.f;
+  for (int b = threadIdx.x >> 5; b < NB; b += 32) {   // one warp per row of the batch tile
+    float s0 = 0.f, s1 = 0.f;
     const long long id = b < B ? ids[static_cast<long long>(b) * ids_stride + *pos_ptr] : 0;
     for (int c = lane * 4; c < D; c += 128) {
-      // (rows past the batch are kept at zero: the residual epilogues update all 32 rows)
+      // (rows past the batch are kept at zero: the residual epilogues update all rows of the tile)
       const float4 v = b < B ? __ldg(reinterpret_cast<const float4*>(W + id * D + c)) : make_float4(0.f, 0.f, 0.f, 0.f);
       *reinterpret_cast<float4*>(x1 + static_cast<long long>(b) * D + c) = v;
       *reinterpret_cast<float4*>(x2 + static_cast<long long>(b) * D + c) = v;
       s0 += (v.x + v.y) + (v.z + v.w);
       s1 += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
     }
+    s0 = warp_sum(s0);
+    s1 = warp_sum(s1);
+    if (lane == 0) { stats[b * 2] = s0; stats[b * 2 + 1] = s1; }
   }
-  s0 = warp_sum(s0);
-  s1 = warp_sum(s1);
-  if (lane == 0) { stats[b * 2] = s0; stats[b * 2 + 1] = s1; }
 }
 
 // ---- launchers ----------------------------------------------------------------------------------
@@ -542,17 +550,26 @@ static int launch_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, int cluster
   return cudaLaunchKernelEx(&cfg, kern, args...) == cudaSuccess ? 0 : -82;
 }
 
-template <int EPI, int PRO>
-static int launch_dec_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const DecGemmArgs& a, int n_tiles, bool pdl,
-                           cudaStream_t st) {
-  auto kern = dec_gemm_kernel<EPI, PRO>;
-  const size_t smem = static_cast<size_t>(a.ks / 64) * (16384 + 4096) + DG_NB * DG_PART_LD * 4 + 1024;
-  static size_t configured = 0;
-  if (smem > configured) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return -81;
-    configured = 200 * 1024;
+template <int EPI, int PRO, int NB>
+static int launch_dec_gemm_nb(const CUtensorMap& tw, const CUtensorMap& tx, const DecGemmArgs& a, int n_tiles, bool pdl,
+                              cudaStream_t st) {
+  auto kern = dec_gemm_kernel<EPI, PRO, NB>;
+  const size_t smem = static_cast<size_t>(a.ks / 64) * (16384 + NB * 128) + NB * DG_PART_LD * 4 + 1024;
+  // largest request: a 512-wide K slice (8 k-blocks) - dynamic + ~1 KB of static shared memory must stay under 227 KB
+  constexpr int kMaxSmem = DG_MAX_KB * (16384 + NB * 128) + NB * DG_PART_LD * 4 + 1024;
+  if (smem > static_cast<size_t>(kMaxSmem)) return -87;
+  static bool configured = false;
+  if (!configured) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem) != cudaSuccess) return -81;
+    configured = true;
   }
   return launch_pdl(kern, dim3(n_tiles * a.ksplit), dim3(DG_THREADS), smem, a.ksplit, pdl, st, tw, tx, a);
+}
+template <int EPI, int PRO>
+static int launch_dec_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const DecGemmArgs& a, int n_tiles, bool pdl,
+                           cudaStream_t st, int nb) {
+  return nb == 64 ? launch_dec_gemm_nb<EPI, PRO, 64>(tw, tx, a, n_tiles, pdl, st)
+                  : launch_dec_gemm_nb<EPI, PRO, 32>(tw, tx, a, n_tiles, pdl, st);
 }
 
 static bool g_dec_pdl = true;
@@ -566,8 +583,8 @@ extern "C" int b200_decode2_gemm(int kind, const void* W, int N, int K, const vo
                                  const float* stats_in, const float* ln_w, const float* ln_b, void* ring,
                                  const int* pos_ptr, int T, int F, float eps, const float* bias, const float* scale,
                                  float* xout, float* stats_out, void* out, int ldo, const void* rot, int q_cols,
-                                 float q_scale, void* stream) {
-  if (K % 64) return -80;
+                                 float q_scale, int nb, void* stream) {
+  if (K % 64 || (nb != 32 && nb != 64)) return -80;
   int ksplit = 8;
   const int max_split = kind == DG_GEGLU ? 4 : 8;
   // enough CTAs to fill the machine, K slices of at most 512, feature ownership in groups of 16
@@ -588,17 +605,17 @@ extern "C" int b200_decode2_gemm(int kind, const void* W, int N, int K, const vo
   if (rc) return rc;
   const bool ln = kind == DG_QKV || kind == DG_GEGLU;
   if (!ln) {
-    rc = make_tmap_bf16_2d(&tx, xin_bf16, DG_NB, K, K, 64, DG_NB);
+    rc = make_tmap_bf16_2d(&tx, xin_bf16, nb, K, K, 64, nb);
     if (rc) return rc;
   } else {
     tx = tw;
   }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   switch (kind) {
-    case DG_QKV: return launch_dec_gemm<DG_QKV, DP_LN>(tw, tx, a, tiles, g_dec_pdl, st);
-    case DG_RESID: return launch_dec_gemm<DG_RESID, DP_TMA>(tw, tx, a, tiles, g_dec_pdl, st);
-    case DG_GEGLU: return launch_dec_gemm<DG_GEGLU, DP_LN>(tw, tx, a, tiles, g_dec_pdl, st);
-    case DG_LOGITS: return launch_dec_gemm<DG_LOGITS, DP_TMA>(tw, tx, a, tiles, g_dec_pdl, st);
+    case DG_QKV: return launch_dec_gemm<DG_QKV, DP_LN>(tw, tx, a, tiles, g_dec_pdl, st, nb);
+    case DG_RESID: return launch_dec_gemm<DG_RESID, DP_TMA>(tw, tx, a, tiles, g_dec_pdl, st, nb);
+    case DG_GEGLU: return launch_dec_gemm<DG_GEGLU, DP_LN>(tw, tx, a, tiles, g_dec_pdl, st, nb);
+    case DG_LOGITS: return launch_dec_gemm<DG_LOGITS, DP_TMA>(tw, tx, a, tiles, g_dec_pdl, st, nb);
     default: return -83;
   }
 }
@@ -625,10 +642,10 @@ extern "C" int b200_decode2_attn(const void* qkv, void* kcache, void* vcache, vo
 }
 
 extern "C" int b200_decode2_embed(const long long* ids, int ids_stride, const float* W, float* x1, float* x2,
-                                  float* stats, int n_sites, const int* pos_ptr, int B, int D, void* stream) {
-  if (B > 32 || D % 128) return -86;
+                                  float* stats, int n_sites, const int* pos_ptr, int B, int D, int nb, void* stream) {
+  if ((nb != 32 && nb != 64) || B > nb || D % 128) return -86;
   dec_embed2_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(ids, ids_stride, W, x1, x2, stats, n_sites,
-                                                                            pos_ptr, B, D);
+                                                                            pos_ptr, B, D, nb);
   return cudaGetLastError() == cudaSuccess ? 0 : -70;
 }
 

@@ -137,9 +137,9 @@ class _Sigs:
     b200_decode_attn = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
     b200_decode_sample = [_p, _i, _i, _f, _i, _f, _p, _p, _i, _l, _p, _i, _p, _i, _i, _p]
     b200_decode_advance = [_p, _p]
-    b200_decode2_gemm = [_i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _i, _f, _p, _p, _p, _p, _p, _i, _p, _i, _f, _p]
+    b200_decode2_gemm = [_i, _p, _i, _i, _p, _p, _p, _p, _p, _p, _p, _i, _i, _f, _p, _p, _p, _p, _p, _i, _p, _i, _f, _i, _p]
     b200_decode2_attn = [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]
-    b200_decode2_embed = [_p, _i, _p, _p, _p, _p, _i, _p, _i, _i, _p]
+    b200_decode2_embed = [_p, _i, _p, _p, _p, _p, _i, _p, _i, _i, _i, _p]
     b200_decode2_set_pdl = [_i]
     b200_attn_bwd = [_p, _p, _p, _p, _p, _p, _p, _p, _p, _f, _i, _i, _i, _i, _i, _i, _i, _p]
 

@@ -173,7 +173,7 @@ int b200_decode_sample(const void* logits, int ld, int n, float temperature, int
 int b200_decode_advance(int* pos_ptr, void* stream);
 
 /* Second-generation decode step (decode2.cu): skinny tcgen05 GEMMs with the weights on the M side and the batch
- * (<= 32 rows, buffers allocated with 32) on an N = 32 tile, K split over a thread-block cluster and reduced through
+ * (<= 64 rows, buffers allocated with nb = 32 or 64 rows) on an N = 32 tile, K split over a thread-block cluster and reduced through
  * distributed shared memory; layer norm + token shift as the prologue of the QKV / FF1 GEMMs (row statistics left
  * behind by the producer of the residual stream); attention over a sparsity-aware cache of `slots` keys per layer
  * (text + one image row | transposed image | conv_half + 1 rows).  All launched with programmatic dependent launch.
@@ -182,11 +182,12 @@ int b200_decode_advance(int* pos_ptr, void* stream);
 int b200_decode2_gemm(int kind, const void* W, int N, int K, const void* xin_bf16, const float* x,
                       const float* stats_in, const float* ln_w, const float* ln_b, void* ring, const int* pos_ptr, int T,
                       int F, float eps, const float* bias, const float* scale, float* xout, float* stats_out, void* out,
-                      int ldo, const void* rot, int q_cols, float q_scale, void* stream);
+                      int ldo, const void* rot, int q_cols, float q_scale, int nb /* batch tile: 32 or 64 rows */,
+                      void* stream);
 int b200_decode2_attn(const void* qkv, void* kcache, void* vcache, void* out, const int* pos_ptr, int B, int H, int T,
                       int F, int mode, int conv_kernel, int slots, void* stream);
 int b200_decode2_embed(const long long* ids, int ids_stride, const float* W, float* x1, float* x2, float* stats,
-                       int n_sites, const int* pos_ptr, int B, int D, void* stream);
+                       int n_sites, const int* pos_ptr, int B, int D, int nb, void* stream);
 int b200_decode2_set_pdl(int on);
 
 /* b200_lamb_step for callers that cannot provide scratch memory.  No counterpart in the reference: it exists for

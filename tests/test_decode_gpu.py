@@ -114,40 +114,42 @@ def _skinny(kind, W, N, K, **kw):
     rc = L.b200_decode2_gemm(kind, W.data_ptr(), N, K, ptr(g("xin")), ptr(g("x")), ptr(g("stats")), ptr(g("ln_w")),
                              ptr(g("ln_b")), ptr(g("ring")), g("pos").data_ptr(), g("T") or 32, g("F") or 16, 1e-5,
                              ptr(g("bias")), ptr(g("scale")), ptr(g("xout")), ptr(g("stats_out")), ptr(g("out")),
-                             g("ldo") or 0, ptr(g("rot")), g("q_cols") or 0, g("q_scale") or 1.0,
+                             g("ldo") or 0, ptr(g("rot")), g("q_cols") or 0, g("q_scale") or 1.0, g("nb") or 32,
                              torch.cuda.current_stream().cuda_stream)
     assert rc == 0, rc
     torch.cuda.synchronize()
 
 
+@pytest.mark.parametrize("nb", [32, 64])
 @pytest.mark.parametrize("N,K", [(1024, 1024), (1024, 4096), (256, 256), (8192, 1024)])
-def test_skinny_gemm_residual_and_logits(N, K):
+def test_skinny_gemm_residual_and_logits(N, K, nb):
     """TMA-operand forms at the production shapes (out-proj K=1024 / 8 splits of 128, FF2 K=4096 / 8 splits of 512, the
     head N=8192) against fp32 matmul; the residual form also leaves the row statistics of its result behind."""
     g = torch.Generator(device="cuda").manual_seed(N + K)
     W = (torch.randn(N, K, device="cuda", generator=g) * K ** -0.5).to(torch.bfloat16)
-    xin = torch.zeros(32, K, device="cuda", dtype=torch.bfloat16)
-    xin[:29] = torch.randn(29, K, device="cuda", generator=g).to(torch.bfloat16)
+    xin = torch.zeros(nb, K, device="cuda", dtype=torch.bfloat16)
+    xin[:nb - 3] = torch.randn(nb - 3, K, device="cuda", generator=g).to(torch.bfloat16)
     bias = torch.randn(N, device="cuda", generator=g)
     scale = torch.rand(N, device="cuda", generator=g) + 0.5
     pos = torch.zeros(1, dtype=torch.int32, device="cuda")
     ref = xin.float() @ W.float().t() + bias
-    x0 = torch.randn(32, N, device="cuda", generator=g)
+    x0 = torch.randn(nb, N, device="cuda", generator=g)
     xout = x0.clone()
-    stats = torch.zeros(32, 2, device="cuda")
-    _skinny(1, W, N, K, xin=xin, bias=bias, scale=scale, xout=xout, stats_out=stats, pos=pos)
+    stats = torch.zeros(nb, 2, device="cuda")
+    _skinny(1, W, N, K, xin=xin, bias=bias, scale=scale, xout=xout, stats_out=stats, pos=pos, nb=nb)
     want = x0 + scale * ref
     assert (xout - want).abs().max().item() < 2e-2
     assert torch.allclose(stats[:, 0], xout.sum(1), rtol=1e-4, atol=1e-2)
     assert torch.allclose(stats[:, 1], (xout * xout).sum(1), rtol=1e-4, atol=1e-2)
-    out = torch.zeros(32, N, device="cuda", dtype=torch.bfloat16)
-    _skinny(3, W, N, K, xin=xin, bias=bias, out=out, ldo=N, pos=pos)
+    out = torch.zeros(nb, N, device="cuda", dtype=torch.bfloat16)
+    _skinny(3, W, N, K, xin=xin, bias=bias, out=out, ldo=N, pos=pos, nb=nb)
     assert (out.float() - ref).abs().max().item() < 3e-2 * max(1.0, ref.abs().max().item())
 
 
+@pytest.mark.parametrize("nb", [32, 64])
 @pytest.mark.parametrize("D", [1024, 256])
 @pytest.mark.parametrize("pos_kind", ["text", "image_first_col", "image_inner"])
-def test_skinny_gemm_layernorm_prologue(D, pos_kind):
+def test_skinny_gemm_layernorm_prologue(D, pos_kind, nb):
     """QKV (rotary epilogue) and GEGLU forms: layer norm from the (sum, sum of squares) left by the producer, token
     shift from the 64-slot ring, against the same statement in fp32 PyTorch."""
     from dalle_b200.models.rotary import rotary_pair_table
@@ -158,11 +160,11 @@ def test_skinny_gemm_layernorm_prologue(D, pos_kind):
     T, F = cfg.text_len, cfg.image_fmap_size
     p = {"text": 9, "image_first_col": T + 3 * F, "image_inner": T + 3 * F + 5}[pos_kind]
     g = torch.Generator(device="cuda").manual_seed(D + p)
-    x = torch.zeros(32, D, device="cuda")
-    x[:30] = torch.randn(30, D, device="cuda", generator=g) * 2 + 0.3
+    x = torch.zeros(nb, D, device="cuda")
+    x[:nb - 2] = torch.randn(nb - 2, D, device="cuda", generator=g) * 2 + 0.3
     stats = torch.stack((x.sum(1), (x * x).sum(1)), dim=1).contiguous()
     ln_w, ln_b = torch.rand(D, device="cuda", generator=g) + 0.5, torch.randn(D, device="cuda", generator=g) * 0.1
-    ring = (torch.randn(32, 64, D // 2, device="cuda", generator=g)).to(torch.bfloat16)
+    ring = (torch.randn(nb, 64, D // 2, device="cuda", generator=g)).to(torch.bfloat16)
     ring0 = ring.clone()
     pos = torch.full((1,), p, dtype=torch.int32, device="cuda")
     # oracle of the prologue
@@ -181,13 +183,13 @@ def test_skinny_gemm_layernorm_prologue(D, pos_kind):
     I = D
     Wq = (torch.randn(3 * I, D, device="cuda", generator=g) * D ** -0.5).to(torch.bfloat16)
     rot = rotary_pair_table(cfg).cuda()
-    out = torch.zeros(32, 3 * I, device="cuda", dtype=torch.bfloat16)
+    out = torch.zeros(nb, 3 * I, device="cuda", dtype=torch.bfloat16)
     _skinny(0, Wq, 3 * I, D, x=x, stats=stats, ln_w=ln_w, ln_b=ln_b, ring=ring, pos=pos, T=T, F=F, out=out, ldo=3 * I,
-            rot=rot, q_cols=I, q_scale=0.125)
-    raw = (hb @ Wq.float().t()).view(32, 3 * I // 2, 2)
+            rot=rot, q_cols=I, q_scale=0.125, nb=nb)
+    raw = (hb @ Wq.float().t()).view(nb, 3 * I // 2, 2)
     cs = rot[p].repeat(3 * I // 64, 1)                       # [pairs of the row, 2]
     ref = torch.stack((raw[..., 0] * cs[:, 0] - raw[..., 1] * cs[:, 1], raw[..., 1] * cs[:, 0] + raw[..., 0] * cs[:, 1]),
-                      dim=-1).view(32, 3 * I)
+                      dim=-1).view(nb, 3 * I)
     ref[:, :I] *= 0.125
     assert (out.float() - ref).abs().max().item() < 3e-2 * max(1.0, ref.abs().max().item())
     # the token's own normalised first half went into the ring, other slots untouched
@@ -198,9 +200,9 @@ def test_skinny_gemm_layernorm_prologue(D, pos_kind):
     hid = 4 * D
     W1 = (torch.randn(2 * hid, D, device="cuda", generator=g) * D ** -0.5).to(torch.bfloat16)
     b1 = torch.randn(2 * hid, device="cuda", generator=g) * 0.1
-    u = torch.zeros(32, hid, device="cuda", dtype=torch.bfloat16)
+    u = torch.zeros(nb, hid, device="cuda", dtype=torch.bfloat16)
     ring.copy_(ring0)
-    _skinny(2, W1, hid, D, x=x, stats=stats, ln_w=ln_w, ln_b=ln_b, ring=ring, pos=pos, T=T, F=F, bias=b1, out=u, ldo=hid)
+    _skinny(2, W1, hid, D, x=x, stats=stats, ln_w=ln_w, ln_b=ln_b, ring=ring, pos=pos, T=T, F=F, bias=b1, out=u, ldo=hid, nb=nb)
     pre = hb @ W1.float().t() + b1
     ref_u = pre[:, :hid] * torch.nn.functional.gelu(pre[:, hid:])
     assert (u.float() - ref_u).abs().max().item() < 3e-2 * max(1.0, ref_u.abs().max().item())
@@ -292,8 +294,8 @@ def test_run_inference_on_the_gpu_goes_through_the_decode_engine(tmp_path):
     assert torch.equal(codes[:32].cuda(), ref[0, :32]), (codes[:32], ref[0, :32])
 
 
-def test_batches_above_32_run_as_concurrent_engines():
-    """generate_images with 40 prompts: slices of 32 + 8 on two engines / streams, interleaved position by position;
+def test_batches_above_64_run_as_concurrent_engines():
+    """generate_images with 70 prompts: slices of 64 + 6 on two engines / streams, interleaved position by position;
     greedy codes of every prompt equal the oracle's (the slices must not disturb each other's caches or position)."""
     cfg = _cfg()
     torch.manual_seed(0)
@@ -303,9 +305,9 @@ def test_batches_above_32_run_as_concurrent_engines():
             p.fill_(0.3)
         model.emb_weight.mul_(4.0)
     model.cuda()
-    text = torch.randint(1, cfg.num_text_tokens, (40, cfg.text_seq_len), device="cuda")
+    text = torch.randint(1, cfg.num_text_tokens, (70, cfg.text_seq_len), device="cuda")
     codes = G.generate_images(model, text, top_k=1, return_codes=True)
-    assert codes.shape == (40, cfg.image_seq_len) and len(model._decode_engines) == 2
+    assert codes.shape == (70, cfg.image_seq_len) and len(model._decode_engines) == 2
     ref = G.generate_codes_reference(model, text, top_k=1, use_cache=True, dtype=torch.float32)
     assert torch.equal(codes[:, :24], ref[:, :24]), (codes[:, :24] != ref[:, :24]).nonzero()[:5]
     assert (codes == ref).float().mean().item() > 0.5

@@ -25,7 +25,7 @@ from dalle_b200.models.decode_engine import DecodeEngine
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--batch", type=int, default=32, help="prompts per engine (<= 64)")
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--eager", action="store_true", help="also time the PyTorch cached decode (40 positions)")
     ap.add_argument("--engines", type=int, default=1, help="concurrent batches per GPU (one engine + stream each)")
