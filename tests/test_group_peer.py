@@ -41,6 +41,36 @@ def test_two_groups_of_two_ranks_and_aux_on_cpu(tmp_path):
     n_params = sum(len(g["params"]) for g in state["training"]["param_groups"])
     assert len([k for k in state["training"]["state"] if k != "local_epoch"]) == n_params
 
+    # (1) the checkpoint a GROUP wrote drives the public inference entry point
+    sys.path.insert(0, os.path.join(ROOT, "inference"))
+    import pickle
+
+    import run_inference
+
+    ckpt = os.path.join(work, "group_model.pt")
+    torch.save(state["model"], ckpt)
+    q = tmp_path / "queries.txt"
+    q.write_text("a cat\n")
+    run_inference.main(["--queries", str(q), "--temperature", "1.0", "--top-k", "4", "--model", ckpt, "--output-dir",
+                        str(tmp_path / "inf"), "--model-preset", "tiny", "--batch-size", "1", "--n-iters", "1"])
+    rec = pickle.load(open(tmp_path / "inf" / "a cat.pickle", "rb"))
+    assert rec["codes"][0].shape == (256,)
+
+    # (2) the group is restarted from its state.zip (alone, no swarm): it resumes at the saved epoch, not at 0
+    saved_epoch = int(state["local_epoch"])
+    assert saved_epoch >= 1
+    log2 = os.path.join(work, "restart.log")
+    cmd2 = _trainer_cmd(work, "peer0", "", "grp_restart", 2, 29950 + os.getpid() % 40, 4)
+    i = cmd2.index("--initial_peers")
+    del cmd2[i:i + 2]
+    p2 = _spawn(cmd2, log2, dict(env, PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""), PYTHONUNBUFFERED="1"), work)
+    assert p2.wait(timeout=400) == 0, open(log2, errors="ignore").read()[-4000:]
+    txt = open(log2, errors="ignore").read()
+    assert "Loaded state" in txt and "Traceback" not in txt, txt[-3000:]
+    epochs = [int(x) for x in re.findall(r"Current epoch: (\d+)", txt)]
+    assert epochs and min(epochs) >= saved_epoch, (saved_epoch, epochs, txt[-3000:])
+    assert len(set(re.findall(r"GROUP_PARAM_CHECKSUM (\S+)", txt))) == 1
+
 
 def _spawn(cmd, log, env, cwd):
     return subprocess.Popen(cmd, stdout=open(log, "w"), stderr=subprocess.STDOUT, env=env, cwd=cwd)
