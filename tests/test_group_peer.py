@@ -89,7 +89,7 @@ def _trainer_cmd(work, name, maddr, prefix, ranks, port, steps, extra=()):
             "--backup_every_steps", "1", "--max_steps", str(steps), *extra]
 
 
-@pytest.mark.timeout(900)
+@pytest.mark.timeout(1200)
 def test_group_nan_rollback_mixed_swarm_and_late_joiner(tmp_path):
     """One swarm with a two-rank group peer and a single-process peer (same averager schema: they average together);
     a NaN is injected into ONE rank of the group, which must roll back as a whole; a second group joins late and
@@ -114,9 +114,9 @@ def test_group_nan_rollback_mixed_swarm_and_late_joiner(tmp_path):
                             aux_log, env, work))
         maddr = _wait_for_maddr(aux_log)
         genv = dict(env, DALLE_B200_INJECT_NAN="1:9")     # rank 1 of the group, after its 9th micro-step
-        procs.append(_spawn(_trainer_cmd(work, "group", maddr, "mix", 2, port, 30), os.path.join(work, "group.log"),
+        procs.append(_spawn(_trainer_cmd(work, "group", maddr, "mix", 2, port, 36), os.path.join(work, "group.log"),
                             genv, work))
-        procs.append(_spawn(_trainer_cmd(work, "single", maddr, "mix", 1, 0, 60), os.path.join(work, "single.log"),
+        procs.append(_spawn(_trainer_cmd(work, "single", maddr, "mix", 1, 0, 80), os.path.join(work, "single.log"),
                             env, work))
         # the late joiner starts once the swarm is a few epochs in
         t0 = time.time()
